@@ -1,0 +1,130 @@
+/*
+ * ffs_oracle.h -- CPU ORACLE for the DIALS dispersion spot-finding hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This is a plain-C restatement of the reference's
+ * CPU algorithm (file:line cited per function in ffs_oracle.c).  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * may load it.  The product library (libffs_b200.so) never links, loads or
+ * calls anything in oracle/.
+ *
+ * Parity status (see DESIGN.md "Oracle"):
+ *   - standard dispersion : PINNED  -- checked bit-for-bit against the
+ *     reference's own baseline/spotfinder/standalone.cc compiled in place
+ *     (oracle/_ref/libffs_ref.so) and against tests/golden/ fixtures produced
+ *     by it.
+ *   - dispersion_extended : parity unpinned -- baseline.cpp needs DIALS/scitbx
+ *     headers which are absent; restated from baseline.cpp:325-813 and
+ *     cross-checked by (a) pass 1 + "b > d" == standard dispersion and
+ *     (b) a brute-force window-sum implementation.
+ *   - connected components: parity unpinned -- Boost.Graph absent; restated
+ *     from connected_components.cc and cross-checked against
+ *     scipy.ndimage.label.
+ */
+#ifndef FFS_ORACLE_H
+#define FFS_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ffs_oracle_params {
+    int32_t kernel_half_x; /* 3  (standalone.cc:16)  */
+    int32_t kernel_half_y; /* 3 */
+    int32_t min_count;     /* 2  (standalone.cc:17)  */
+    double nsig_b;         /* 6  (standalone.cc:19)  */
+    double nsig_s;         /* 3  (standalone.cc:20)  */
+    double threshold;      /* 0  (standalone.cc:18)  */
+} ffs_oracle_params;
+
+/* One connected component ("Reflection3D", connected_components.hpp:31-268). */
+typedef struct ffs_oracle_spot {
+    uint64_t label;          /* canonical label: min (z * width*height + linear index) */
+    uint32_t x_min, x_max, y_min, y_max;
+    int32_t z_min, z_max;
+    uint32_t num_pixels;
+    uint32_t peak_x, peak_y;
+    int32_t peak_z;
+    uint64_t peak_intensity;
+    uint64_t sum_intensity;
+    float com_x, com_y, com_z;      /* center_of_mass(): double math, float storage */
+    float peak_centroid_distance;   /* peak_centroid_distance(): float math        */
+} ffs_oracle_spot;
+
+void ffs_oracle_default_params(ffs_oracle_params *p);
+
+/* image: width*height pixels, bytes_per_pixel 2 (uint16) or 4 (uint32).
+ * mask : width*height bytes, non-zero = valid.
+ * dst  : width*height bytes, written 0/1.
+ * Returns the number of strong pixels, or <0 on argument error.            */
+int64_t ffs_oracle_dispersion(const void *image, int bytes_per_pixel,
+                              const uint8_t *mask, int width, int height,
+                              const ffs_oracle_params *p, uint8_t *dst);
+
+int64_t ffs_oracle_dispersion_extended(const void *image, int bytes_per_pixel,
+                                       const uint8_t *mask, int width, int height,
+                                       const ffs_oracle_params *p, uint8_t *dst);
+
+/* Intermediate planes of the extended algorithm, for stage-by-stage parity.
+ * stage 1: dst = dispersion mask (a > c);  stage 2: dst = eroded mask
+ * (1 = background/valid, 0 = masked or eroded signal core).                */
+int64_t ffs_oracle_extended_stage(const void *image, int bytes_per_pixel,
+                                  const uint8_t *mask, int width, int height,
+                                  const ffs_oracle_params *p, int stage, uint8_t *dst);
+
+/* Brute-force (no summed-area table) versions: exact integer window sums.
+ * Used only to cross-check the SAT restatement on small frames.            */
+int64_t ffs_oracle_dispersion_bruteforce(const void *image, int bytes_per_pixel,
+                                         const uint8_t *mask, int width, int height,
+                                         const ffs_oracle_params *p, uint8_t *dst);
+int64_t ffs_oracle_dispersion_extended_bruteforce(const void *image, int bytes_per_pixel,
+                                                  const uint8_t *mask, int width,
+                                                  int height, const ffs_oracle_params *p,
+                                                  uint8_t *dst);
+
+/* Resolution mask (kernels/masking.cu:37-147), applied in place to a u8 mask. */
+void ffs_oracle_resolution_mask(uint8_t *mask, int width, int height, float wavelength,
+                                float distance_m, float beam_center_x_px,
+                                float beam_center_y_px, float pixel_size_x_m,
+                                float pixel_size_y_m, float dmin, float dmax);
+
+/* Connected components over a stack of n_slices strong planes (n_slices == 1
+ * gives the 2D per-image case with z = 0, connected_components.cc:238-266;
+ * n_slices > 1 the 3D case, :270-470).
+ *   strong      : n_slices * width*height bytes (non-zero = strong)
+ *   image       : n_slices * width*height pixels
+ *   row_wrap    : 1 = reproduce the reference's "linear_index + 1" link without a
+ *                 row-wrap check (connected_components.cc:62-70); 0 = true 4-conn.
+ *   labels_out  : optional, n_slices*width*height int64; -1 for non-strong, else the
+ *                 component's canonical label (min z*px + linear index).
+ *   spots_out   : optional array of capacity max_spots; components in ascending
+ *                 canonical-label order (== Boost label order), UNFILTERED.
+ * Returns number of components (may exceed max_spots; only max_spots written). */
+int64_t ffs_oracle_connected_components(const uint8_t *strong, const void *image,
+                                        int bytes_per_pixel, int width, int height,
+                                        int n_slices, int row_wrap, int64_t *labels_out,
+                                        ffs_oracle_spot *spots_out, int64_t max_spots);
+
+/* filter_reflections (connected_components.cc:207-236): stable in-place filter.
+ * Returns the number kept; n_removed_size / n_removed_sep may be NULL.       */
+int64_t ffs_oracle_filter_spots(ffs_oracle_spot *spots, int64_t n, uint32_t min_spot_size,
+                                float max_peak_centroid_separation,
+                                int64_t *n_removed_size, int64_t *n_removed_sep);
+
+/* Whole per-image hot path on the CPU, as the reference frame loop does it
+ * (spotfinder.cc:859-928): threshold -> CC -> boxes (min-size filter) ->
+ * find_2d_components (both filters).  Used as the timed CPU baseline "port".
+ * Outputs: counts[0]=num_strong_pixels, [1]=n_spots_total (boxes),
+ *          [2]=num_strong_pixels_filtered, [3]=n_spots after both filters.   */
+int ffs_oracle_process_frame(const void *image, int bytes_per_pixel, const uint8_t *mask,
+                             int width, int height, const ffs_oracle_params *p,
+                             int algorithm, uint32_t min_spot_size,
+                             float max_peak_centroid_separation, int row_wrap,
+                             int64_t counts[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
