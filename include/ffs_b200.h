@@ -1,0 +1,233 @@
+/*
+ * ffs_b200.h -- C ABI of libffs_b200.so, the B200-native (sm_100a) implementation of
+ * fast-feedback-service's DIALS dispersion spot-finding hot path.
+ *
+ * The reference has no in-process plugin boundary for this path: its replaceable
+ * seams are two launch wrappers, one host class and one CPU C API.  Each entry point
+ * below names the reference interface it replaces (paths relative to the reference
+ * tree).  All functions return 0 (FFS_OK) or a negative ffs_status; no exception
+ * crosses the ABI; no torch / C++ type appears in a signature.
+ *
+ *   reference seam                                              replaced by
+ *   ----------------------------------------------------------  -------------------------------
+ *   call_do_spotfinding_dispersion   spotfinder/spotfinder.cuh:9-20   ffs_threshold / ffs_process
+ *   call_do_spotfinding_extended     spotfinder/spotfinder.cuh:22-34  ffs_threshold / ffs_process
+ *                                                                     (params.algorithm = 1)
+ *   upload_mask                      spotfinder/spotfinder.cc:62-108  ffs_create (mask argument)
+ *   apply_resolution_filtering       spotfinder/spotfinder.cc:110-137 ffs_apply_resolution_mask
+ *   call_apply_resolution_mask       spotfinder/kernels/masking.cuh:92-97
+ *   ConnectedComponents ctor/get_boxes/find_2d_components
+ *        spotfinder/connected_components/connected_components.hpp:299-397
+ *                                                                     ffs_process + ffs_fetch
+ *   ConnectedComponents::find_3d_components  (same header)            ffs_sweep_*
+ *   per-thread frame loop (pinned buffers, H2D, kernels, D2H, CC)
+ *        spotfinder/spotfinder.cc:725-1092                            ffs_acquire / ffs_submit /
+ *                                                                     ffs_wait  (streaming API)
+ *   spotfinder_create / _free / _standard_dispersion
+ *        baseline/spotfinder/baseline.h:9-13                          same names (shim section)
+ *
+ * Data conventions
+ *   frame      : width*height pixels, row-major, uint16 or uint32 (bytes_per_pixel 2|4),
+ *                dense on the host; on the device rows are padded to a 128-byte pitch.
+ *   mask       : width*height bytes, non-zero = valid (VALID_PIXEL = 1, include/common.hpp).
+ *   strong bits: 1 bit per pixel, bit (x & 7) of byte y*ceil(width/8) + (x >> 3) on the
+ *                host side (numpy.unpackbits(..., bitorder="little") row by row).
+ *   spots      : ascending canonical label = minimum (z, linear index) of the component,
+ *                which is the order boost::connected_components gives the reference
+ *                (connected_components.cc:241-252,396-399).
+ */
+#ifndef FFS_B200_H
+#define FFS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FFS_ALGO_DISPERSION 0          /* DispersionThreshold,         standalone.cc:27-206  */
+#define FFS_ALGO_DISPERSION_EXTENDED 1 /* DispersionExtendedThreshold, baseline.cpp:325-813  */
+
+typedef enum ffs_status {
+    FFS_OK = 0,
+    FFS_ERR_ARG = -1,      /* bad argument                                     */
+    FFS_ERR_CUDA = -2,     /* CUDA runtime/driver error (see ffs_last_error)   */
+    FFS_ERR_NO_DEVICE = -3,/* no CUDA device / wrong architecture              */
+    FFS_ERR_CAPACITY = -4, /* a per-frame capacity (strong pixels, spots) hit  */
+    FFS_ERR_STATE = -5,    /* call sequence error (slot busy, nothing pending) */
+    FFS_ERR_NOMEM = -6
+} ffs_status;
+
+typedef struct ffs_ctx ffs_ctx;
+
+typedef struct ffs_params {
+    uint32_t width;           /* fast axis, pixels                                              */
+    uint32_t height;          /* slow axis                                                      */
+    uint32_t bytes_per_pixel; /* 2 (spotfinder) or 4 (spotfinder32, PIXEL_DATA_32BIT)           */
+    int32_t algorithm;        /* FFS_ALGO_*                                                     */
+    int32_t kernel_half;      /* 3 => 7x7 window (standalone.cc:16; KERNEL_RADIUS)              */
+    int32_t min_count;        /* 2 (standalone.cc:17)                                           */
+    double nsig_b;            /* 6 (standalone.cc:19)                                           */
+    double nsig_s;            /* 3 (standalone.cc:20)                                           */
+    double threshold;         /* 0 (standalone.cc:18)                                           */
+    uint32_t min_spot_size;   /* 3   (--min-spot-size,    spotfinder.cc:324)                    */
+    uint32_t min_spot_size_3d;/* 3   (--min-spot-size-3d, spotfinder.cc:330)                    */
+    float max_peak_centroid_separation; /* 2.0 (spotfinder.cc:336)                              */
+    int32_t cc_row_wrap;      /* 1 = link index k and k+1 with no row-wrap check, exactly as
+                                 connected_components.cc:62-70 does; 0 = true 4-connectivity     */
+    int32_t device;           /* CUDA device ordinal (-d/--device, cuda_arg_parser.cc:30)       */
+    int32_t n_slots;          /* frames resident on the device at once (batch / ring depth)     */
+    uint32_t max_strong_per_frame; /* capacity of the per-frame strong-pixel list (0 = default) */
+    uint32_t max_spots_per_frame;  /* capacity of the per-frame spot list         (0 = default) */
+} ffs_params;
+
+/* One connected component.  Mirrors Reflection3D (connected_components.hpp:31-268):
+ * bbox, pixel count, centre of mass (double math, float storage, +0.5 pixel-centre
+ * offset, hpp:71-103), peak pixel (max intensity, ties -> smallest (z, y, x),
+ * connected_components.cc:143-157) and peak-centroid distance (float math, hpp:111-206). */
+typedef struct ffs_spot {
+    uint64_t label; /* min (z * width*height + y*width + x) over the component */
+    uint32_t x_min, x_max, y_min, y_max;
+    int32_t z_min, z_max;
+    uint32_t num_pixels;
+    uint32_t peak_x, peak_y;
+    int32_t peak_z;
+    uint64_t peak_intensity;
+    uint64_t sum_intensity;
+    float com_x, com_y, com_z;
+    float peak_centroid_distance;
+} ffs_spot;
+
+/* Per-frame counters, as the reference frame loop reports them (spotfinder.cc:905-909,
+ * 997-1005):  num_strong_pixels = all strong pixels; n_spots_total = boxes that survive
+ * the min_spot_size filter only; num_strong_pixels_filtered = pixels in those boxes;
+ * n_spots_filtered = spots that also survive the peak-centroid filter (find_2d_components). */
+typedef struct ffs_frame_result {
+    uint64_t frame_id;
+    uint32_t num_strong_pixels;
+    uint32_t n_components; /* before any filter */
+    uint32_t n_spots_total;
+    uint32_t num_strong_pixels_filtered;
+    uint32_t n_spots_filtered;
+    int32_t status; /* FFS_OK or FFS_ERR_CAPACITY for this frame */
+} ffs_frame_result;
+
+/* ---- lifetime ----------------------------------------------------------------------- */
+void ffs_default_params(ffs_params *p);
+/* mask: width*height bytes (non-zero = valid) or NULL for "all valid" (upload_mask,
+ * spotfinder.cc:62-108). */
+int ffs_create(const ffs_params *p, const uint8_t *mask, ffs_ctx **out);
+void ffs_destroy(ffs_ctx *ctx);
+const char *ffs_last_error(const ffs_ctx *ctx); /* NULL ctx: last ffs_create error */
+const char *ffs_version(void);
+/* Number of CUDA devices, and "<name> (CUDA M.m)" for --list-devices
+ * (cuda_arg_parser.cc:38-53). */
+int ffs_device_count(void);
+int ffs_device_description(int device, char *buf, size_t buflen);
+
+/* ---- mask ---------------------------------------------------------------------------- */
+/* apply_resolution_mask (kernels/masking.cu:99-147): float math, applied in place to
+ * the device mask; dmin/dmax <= 0 disable that bound.  Units as the kernel takes them:
+ * distance and pixel sizes in metres, beam centre in pixels, wavelength in Angstrom. */
+int ffs_apply_resolution_mask(ffs_ctx *ctx, float wavelength, float distance_m,
+                              float beam_center_x_px, float beam_center_y_px,
+                              float pixel_size_x_m, float pixel_size_y_m, float dmin, float dmax);
+int ffs_get_mask(ffs_ctx *ctx, uint8_t *mask_out); /* width*height bytes, 0/1 */
+uint64_t ffs_mask_valid_count(ffs_ctx *ctx);
+
+/* ---- device-resident (slot) API: the kernels with inputs already in HBM --------------- */
+/* Copy n dense host frames into device slots first_slot.. (synchronous). */
+int ffs_upload(ffs_ctx *ctx, int first_slot, int n, const void *host_frames);
+/* Threshold only: slots -> strong bit-planes.  stream: a cudaStream_t passed as void*
+ * (NULL = the context's own stream).  Asynchronous on that stream. */
+int ffs_threshold(ffs_ctx *ctx, int first_slot, int n, void *stream);
+/* Whole device path: threshold -> connected components -> spot reduction -> filters. */
+int ffs_process(ffs_ctx *ctx, int first_slot, int n, void *stream);
+/* Wait for everything queued on `stream` (or the context stream). */
+int ffs_sync(ffs_ctx *ctx, void *stream);
+/* Parity hooks (synchronous). */
+int ffs_get_strong_bits(ffs_ctx *ctx, int slot, uint8_t *bits_out /* height*ceil(width/8) */);
+int ffs_get_strong_u8(ffs_ctx *ctx, int slot, uint8_t *plane_out /* width*height, 0/1 */);
+/* Extended algorithm intermediates: stage 1 = first-pass dispersion mask, stage 2 =
+ * eroded plane (1 = valid pixel outside the signal core).  width*height bytes. */
+int ffs_get_extended_stage_u8(ffs_ctx *ctx, int slot, int stage, uint8_t *plane_out);
+/* Results of ffs_process for one slot.  spots may be NULL; at most max_spots written, in
+ * canonical order, UNFILTERED (use the flags below or ffs_frame_result counts).
+ * *n_spots receives the number of components. */
+int ffs_fetch(ffs_ctx *ctx, int slot, ffs_frame_result *result, ffs_spot *spots,
+              size_t max_spots, size_t *n_spots);
+/* Canonical label per pixel (int64, -1 = not strong), for label parity. */
+int ffs_get_labels(ffs_ctx *ctx, int slot, int64_t *labels_out /* width*height */);
+
+/* ---- streaming API: host frames in, per-frame results out ------------------------------ */
+/* The pinned-host ring of the reference's frame loop (spotfinder.cc:729-742), shared by
+ * all producer threads.  ffs_acquire blocks until a ring slot is free and returns its
+ * pinned buffer; the caller fills it (reader / decompressor output) and calls ffs_submit,
+ * which queues H2D + kernels + the small result D2H on one of the context's streams.
+ * ffs_wait blocks for the oldest submitted frame and returns its result.  Thread-safe. */
+int ffs_acquire(ffs_ctx *ctx, int *slot, void **pinned_pixels);
+int ffs_submit(ffs_ctx *ctx, int slot, uint64_t frame_id);
+/* Convenience: acquire + memcpy from a pageable buffer + submit. */
+int ffs_submit_copy(ffs_ctx *ctx, uint64_t frame_id, const void *pixels);
+/* spots/max_spots/n_spots as in ffs_fetch; returns FFS_ERR_STATE if nothing is pending. */
+int ffs_wait(ffs_ctx *ctx, ffs_frame_result *result, ffs_spot *spots, size_t max_spots,
+             size_t *n_spots);
+int ffs_pending(ffs_ctx *ctx);
+
+/* ---- rotation sweeps: 3D connected components (find_3d_components) ---------------------- */
+/* Frames processed with sweep recording on keep their strong-pixel lists on the device;
+ * ffs_sweep_finish labels the whole stack (6-connectivity: index+1, index+width, same
+ * index in the next slice, connected_components.cc:316-370), z = position of the frame
+ * in ascending frame_id order (cc:409,441), and returns all components UNFILTERED in
+ * canonical order.  The caller frees *spots with ffs_free. */
+int ffs_sweep_begin(ffs_ctx *ctx, uint64_t max_frames);
+int ffs_sweep_finish(ffs_ctx *ctx, ffs_spot **spots, size_t *n_spots);
+/* Boundary exchange for slab-sharded sweeps (one slab of consecutive frames per GPU).
+ * ffs_sweep_export_plane packs the strong pixels of the slab's first (which=0) or last
+ * (which=1) frame as {uint32 linear index, uint32 local component id}; a neighbour rank
+ * intersects it with its own boundary plane (ffs_sweep_match_plane) to get cross-slab
+ * equivalence pairs.  Partial per-component sums are merged by the caller (see
+ * ffs_b200.sweep in the Python host layer). */
+int ffs_sweep_export_plane(ffs_ctx *ctx, int which, uint32_t **index_and_component,
+                           size_t *n_pixels);
+void ffs_free(void *p);
+
+/* filter_reflections (connected_components.cc:207-236): stable, in place; returns kept. */
+size_t ffs_filter_spots(ffs_spot *spots, size_t n, uint32_t min_spot_size,
+                        float max_peak_centroid_separation, size_t *n_removed_size,
+                        size_t *n_removed_separation);
+
+/* ---- instrumentation --------------------------------------------------------------------- */
+/* Number of kernels this library has launched since ffs_create (all streams). */
+uint64_t ffs_kernel_launches(const ffs_ctx *ctx);
+/* Device pitch (bytes) of a frame row / bytes of one device frame / of one bit-plane. */
+size_t ffs_frame_pitch(const ffs_ctx *ctx);
+size_t ffs_frame_bytes_device(const ffs_ctx *ctx);
+
+/* ---- baseline.h-compatible shim (baseline/spotfinder/baseline.h:9-13) -------------------- */
+/* image_t as h5read/include/h5read.h:34-39 declares it; image_t_type is uint16_t here
+ * (uint32_t when the caller was built with PIXEL_DATA_32BIT: use the *32 entry points). */
+#ifdef __cplusplus
+typedef bool ffs_bool;
+#else
+typedef _Bool ffs_bool;
+#endif
+typedef struct ffs_image_t {
+    void *data;    /* image_t_type*  */
+    uint8_t *mask; /* 1 = valid      */
+    size_t slow;
+    size_t fast;
+} ffs_image_t;
+void *spotfinder_create(size_t width, size_t height);
+void spotfinder_free(void *context);
+/* Returns the number of strong pixels; *destination borrows context-owned storage
+ * (width*height bool) valid until the next call on the context. */
+uint32_t spotfinder_standard_dispersion(void *context, ffs_image_t *image, ffs_bool **destination);
+void *spotfinder_create32(size_t width, size_t height);
+uint32_t spotfinder_standard_dispersion32(void *context, ffs_image_t *image, ffs_bool **destination);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FFS_B200_H */
