@@ -1,0 +1,329 @@
+// api_core.inl -- lifetime, mask, slot upload, threshold launch, parity hooks.
+
+static constexpr int kThreshStages = 3;
+static constexpr int kThreshWarps = 4;
+
+extern "C" void ffs_default_params(ffs_params* p) {
+    if (!p) return;
+    memset(p, 0, sizeof(*p));
+    p->bytes_per_pixel = 2;
+    p->algorithm = FFS_ALGO_DISPERSION;
+    p->kernel_half = 3;
+    p->min_count = 2;
+    p->nsig_b = 6.0;
+    p->nsig_s = 3.0;
+    p->threshold = 0.0;
+    p->min_spot_size = 3;
+    p->min_spot_size_3d = 3;
+    p->max_peak_centroid_separation = 2.0f;
+    p->cc_row_wrap = 1;
+    p->device = 0;
+    p->n_slots = 4;
+}
+
+extern "C" const char* ffs_version(void) { return "ffs_b200 0.1.0 (sm_100a)"; }
+
+extern "C" const char* ffs_last_error(const ffs_ctx* ctx) {
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int ffs_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" int ffs_device_description(int device, char* buf, size_t buflen) {
+    cudaDeviceProp prop;
+    if (!buf || cudaGetDeviceProperties(&prop, device) != cudaSuccess) return FFS_ERR_ARG;
+    snprintf(buf, buflen, "%s (CUDA %d.%d)", prop.name, prop.major, prop.minor);
+    return FFS_OK;
+}
+
+static int repack_mask(ffs_ctx* c) {
+    const long long words = (long long)(c->bits_pitch / 4) * c->p.height;
+    FFS_CK(c, cudaMemsetAsync(c->d_valid_count, 0, sizeof(unsigned long long), c->stream));
+    pack_mask_kernel<<<(unsigned)((words + 255) / 256), 256, 0, c->stream>>>(
+      c->d_mask, (int)c->p.width, (int)c->p.height, reinterpret_cast<uint32_t*>(c->d_valid_bits),
+      c->bits_pitch, c->d_valid_count);
+    c->launches++;
+    unsigned long long n = 0;
+    FFS_CK(c, cudaMemcpyAsync(&n, c->d_valid_count, sizeof(n), cudaMemcpyDeviceToHost, c->stream));
+    FFS_CK(c, cudaStreamSynchronize(c->stream));
+    c->valid_count = n;
+    return FFS_OK;
+}
+
+static int create_impl(ffs_ctx* c, const uint8_t* mask) {
+    const ffs_params& p = c->p;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        c->err = "no CUDA device: libffs_b200 has no CPU fallback";
+        return FFS_ERR_NO_DEVICE;
+    }
+    FFS_CK(c, cudaSetDevice(p.device));
+    cudaDeviceProp prop;
+    FFS_CK(c, cudaGetDeviceProperties(&prop, p.device));
+    if (prop.major != 10) {
+        c->err = std::string("device ") + prop.name + " is not sm_100: kernels are built for sm_100a only";
+        return FFS_ERR_NO_DEVICE;
+    }
+    c->sm_count = prop.multiProcessorCount;
+    const size_t px = (size_t)p.width * p.height;
+    c->pitch = round_up((size_t)p.width * p.bytes_per_pixel, 128);
+    c->frame_stride = c->pitch * p.height;
+    c->bits_pitch = round_up((p.width + 7) / 8, 16);
+    c->bits_stride = round_up(c->bits_pitch * p.height, 256);
+    const int window = (2 * p.kernel_half + 1) * (2 * p.kernel_half + 1);
+    c->eff_min_count = p.min_count <= 0 ? window : p.min_count;  // standalone.cc:60-64
+
+    FFS_CK(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    const size_t S = p.n_slots;
+    FFS_CK(c, cudaMalloc(&c->d_mask, px));
+    FFS_CK(c, cudaMalloc(&c->d_valid_bits, c->bits_stride));
+    FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
+    FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
+    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S));
+    FFS_CK(c, cudaMalloc(&c->d_valid_count, sizeof(unsigned long long)));
+    FFS_CK(c, cudaMemset(c->d_frames, 0, c->frame_stride * S));
+    FFS_CK(c, cudaMemset(c->d_strong, 0, c->bits_stride * S));
+    if (p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) {
+        FFS_CK(c, cudaMalloc(&c->d_ext1, c->bits_stride * S));
+        FFS_CK(c, cudaMalloc(&c->d_ext2, c->bits_stride * S));
+        FFS_CK(c, cudaMemset(c->d_ext1, 0, c->bits_stride * S));
+        FFS_CK(c, cudaMemset(c->d_ext2, 0, c->bits_stride * S));
+    }
+    if (mask)
+        FFS_CK(c, cudaMemcpy(c->d_mask, mask, px, cudaMemcpyHostToDevice));
+    else
+        FFS_CK(c, cudaMemset(c->d_mask, 1, px));
+    int rc = repack_mask(c);
+    if (rc) return rc;
+
+    // TMA descriptors: image ring (x, y, slot) and validity bytes (x, y)
+    {
+        const bool p16 = p.bytes_per_pixel == 2;
+        cuuint64_t dims[3] = {p.width, p.height, (cuuint64_t)S};
+        cuuint64_t strides[2] = {c->pitch, c->frame_stride};
+        cuuint32_t box[3] = {p16 ? 256u : 128u, (cuuint32_t)(2 * p.kernel_half + 1), 1};
+        rc = make_tensor_map(c, &c->tm_img, p16 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32,
+                             3, c->d_frames, dims, strides, box);
+        if (rc) return rc;
+        cuuint64_t vdims[2] = {(cuuint64_t)(p.width + 7) / 8, p.height};
+        cuuint64_t vstrides[1] = {c->bits_pitch};
+        cuuint32_t vbox[2] = {p16 ? (cuuint32_t)ThreshGeo<uint16_t, 3, 8>::VROW_BYTES
+                                  : (cuuint32_t)ThreshGeo<uint32_t, 3, 4>::VROW_BYTES,
+                              (cuuint32_t)(2 * p.kernel_half + 1)};
+        rc = make_tensor_map(c, &c->tm_valid, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_valid_bits,
+                             vdims, vstrides, vbox);
+        if (rc) return rc;
+        c->have_tm = true;
+    }
+    rc = extended_setup(c);
+    if (rc) return rc;
+    rc = cc_setup(c);
+    if (rc) return rc;
+    return stream_setup(c);
+}
+
+extern "C" int ffs_create(const ffs_params* p, const uint8_t* mask, ffs_ctx** out) {
+    if (!p || !out) return FFS_ERR_ARG;
+    *out = nullptr;
+    if (p->width == 0 || p->height == 0 || p->width > (uint32_t)kMaxDim ||
+        p->height > (uint32_t)kMaxDim || (p->bytes_per_pixel != 2 && p->bytes_per_pixel != 4) ||
+        p->kernel_half != 3 || p->n_slots < 1 || p->nsig_b < 0 || p->nsig_s < 0 ||
+        p->threshold < 0 ||
+        (p->algorithm != FFS_ALGO_DISPERSION && p->algorithm != FFS_ALGO_DISPERSION_EXTENDED)) {
+        g_create_error = "ffs_create: invalid parameters (kernel_half must be 3, dimensions <= 8192)";
+        return FFS_ERR_ARG;
+    }
+    ffs_ctx* c = new (std::nothrow) ffs_ctx();
+    if (!c) return FFS_ERR_NOMEM;
+    c->p = *p;
+    int rc = create_impl(c, mask);
+    if (rc) {
+        g_create_error = c->err;
+        ffs_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return FFS_OK;
+}
+
+extern "C" void ffs_destroy(ffs_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->p.device);
+    cudaDeviceSynchronize();
+    stream_teardown(c);
+    cc_teardown(c);
+    cudaFree(c->d_mask);
+    cudaFree(c->d_valid_bits);
+    cudaFree(c->d_frames);
+    cudaFree(c->d_strong);
+    cudaFree(c->d_ext1);
+    cudaFree(c->d_ext2);
+    cudaFree(c->d_strong_count);
+    cudaFree(c->d_valid_count);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" uint64_t ffs_kernel_launches(const ffs_ctx* c) { return c ? c->launches.load() : 0; }
+extern "C" size_t ffs_frame_pitch(const ffs_ctx* c) { return c ? c->pitch : 0; }
+extern "C" size_t ffs_frame_bytes_device(const ffs_ctx* c) { return c ? c->frame_stride : 0; }
+extern "C" uint64_t ffs_mask_valid_count(ffs_ctx* c) { return c ? c->valid_count : 0; }
+extern "C" void ffs_free(void* p) { free(p); }
+
+extern "C" int ffs_apply_resolution_mask(ffs_ctx* c, float wavelength, float distance_m, float bcx,
+                                         float bcy, float psx, float psy, float dmin, float dmax) {
+    if (!c) return FFS_ERR_ARG;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    dim3 block(32, 32), grid((c->p.width + 31) / 32, (c->p.height + 31) / 32);  // spotfinder.cc:119-121
+    resolution_mask_kernel<<<grid, block, 0, c->stream>>>(c->d_mask, (int)c->p.width, (int)c->p.height,
+                                                          wavelength, distance_m, bcx, bcy, psx, psy,
+                                                          dmin, dmax);
+    c->launches++;
+    FFS_CK(c, cudaGetLastError());
+    return repack_mask(c);
+}
+
+extern "C" int ffs_get_mask(ffs_ctx* c, uint8_t* out) {
+    if (!c || !out) return FFS_ERR_ARG;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaMemcpy(out, c->d_mask, (size_t)c->p.width * c->p.height, cudaMemcpyDeviceToHost));
+    return FFS_OK;
+}
+
+static bool slots_ok(const ffs_ctx* c, int first, int n) {
+    return c && first >= 0 && n >= 1 && first + n <= c->p.n_slots;
+}
+
+extern "C" int ffs_upload(ffs_ctx* c, int first_slot, int n, const void* host_frames) {
+    if (!slots_ok(c, first_slot, n) || !host_frames) return FFS_ERR_ARG;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+    for (int i = 0; i < n; ++i) {
+        FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)(first_slot + i) * c->frame_stride, c->pitch,
+                                    (const uint8_t*)host_frames + (size_t)i * row * c->p.height, row,
+                                    row, c->p.height, cudaMemcpyHostToDevice, c->stream));
+    }
+    FFS_CK(c, cudaStreamSynchronize(c->stream));
+    return FFS_OK;
+}
+
+// Pick output rows per warp task: R + 2*KH a multiple of the stage depth (7), as large as
+// possible (less halo re-reading) while still giving every SM's warp slots ~2 tasks.
+static int pick_tile_rows(const ffs_ctx* c, int n_frames, int out_cols, int ks, int kh) {
+    const int forced = env_int("FFS_TILE_ROWS", 0);
+    if (forced > 0) return forced;
+    const long long want = 2LL * c->sm_count * 12;
+    const int n_strips = ((int)c->p.width + out_cols - 1) / out_cols;
+    int best = ks * 5 - 2 * kh;
+    for (int groups = 19; groups >= 5; --groups) {
+        const int R = groups * ks - 2 * kh;
+        const long long tasks = (long long)n_frames * n_strips * (((int)c->p.height + R - 1) / R);
+        best = R;
+        if (tasks >= want) break;
+    }
+    return best;
+}
+
+template <typename PixelT, int PPL>
+static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+    using G = ThreshGeo<PixelT, 3, PPL>;
+    auto kern = dispersion_kernel<PixelT, 3, PPL, kThreshStages, kThreshWarps>;
+    const int smem = kThreshWarps * G::smem_per_warp(kThreshStages) + 128;
+    static bool attr_done[64] = {};
+    if (!attr_done[c->p.device & 63]) {
+        FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_done[c->p.device & 63] = true;
+    }
+    ThreshArgs a{};
+    a.width = (int)c->p.width;
+    a.height = (int)c->p.height;
+    a.n_frames = n;
+    a.slot0 = first_slot;
+    a.tile_rows = pick_tile_rows(c, n, G::OUT_COLS, G::KS, 3);
+    a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
+    a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
+    a.image = c->d_frames;
+    a.pitch = c->pitch;
+    a.frame_stride = c->frame_stride;
+    a.valid_bits = c->d_valid_bits;
+    a.valid_pitch = c->bits_pitch;
+    a.strong_bits = reinterpret_cast<uint32_t*>(c->d_strong);
+    a.strong_pitch = c->bits_pitch;
+    a.strong_frame_stride = c->bits_stride;
+    a.strong_count = c->d_strong_count;
+    a.nsig_b = c->p.nsig_b;
+    a.nsig_s = c->p.nsig_s;
+    a.threshold = c->p.threshold;
+    a.min_count = c->eff_min_count;
+    a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
+    const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
+    const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
+    kern<<<grid, kThreshWarps * 32, smem, st>>>(c->tm_img, c->tm_valid, a);
+    c->launches++;
+    FFS_CK(c, cudaGetLastError());
+    return FFS_OK;
+}
+
+static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+    FFS_CK(c, cudaMemsetAsync(c->d_strong + (size_t)first_slot * c->bits_stride, 0,
+                              c->bits_stride * n, st));
+    FFS_CK(c, cudaMemsetAsync(c->d_strong_count + first_slot, 0, sizeof(unsigned) * n, st));
+    if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
+    if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
+    return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);
+}
+
+extern "C" int ffs_threshold(ffs_ctx* c, int first_slot, int n, void* stream) {
+    if (!slots_ok(c, first_slot, n)) return FFS_ERR_ARG;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    return threshold_impl(c, first_slot, n, pick_stream(c, stream));
+}
+
+extern "C" int ffs_sync(ffs_ctx* c, void* stream) {
+    if (!c) return FFS_ERR_ARG;
+    FFS_CK(c, cudaStreamSynchronize(pick_stream(c, stream)));
+    return FFS_OK;
+}
+
+static int get_bits_plane(ffs_ctx* c, const uint8_t* d_plane, uint8_t* out) {
+    const size_t row = (c->p.width + 7) / 8;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaDeviceSynchronize());
+    FFS_CK(c, cudaMemcpy2D(out, row, d_plane, c->bits_pitch, row, c->p.height, cudaMemcpyDeviceToHost));
+    return FFS_OK;
+}
+
+static int get_u8_plane(ffs_ctx* c, const uint8_t* d_plane, uint8_t* out) {
+    const size_t px = (size_t)c->p.width * c->p.height;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaDeviceSynchronize());
+    uint8_t* tmp = nullptr;
+    FFS_CK(c, cudaMalloc(&tmp, px));
+    unpack_bits_kernel<<<(unsigned)((px + 255) / 256), 256, 0, c->stream>>>(
+      reinterpret_cast<const uint32_t*>(d_plane), c->bits_pitch, (int)c->p.width, (int)c->p.height, tmp);
+    c->launches++;
+    cudaError_t e = cudaMemcpyAsync(out, tmp, px, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(tmp);
+    FFS_CK(c, e);
+    return FFS_OK;
+}
+
+extern "C" int ffs_get_strong_bits(ffs_ctx* c, int slot, uint8_t* out) {
+    if (!slots_ok(c, slot, 1) || !out) return FFS_ERR_ARG;
+    return get_bits_plane(c, c->d_strong + (size_t)slot * c->bits_stride, out);
+}
+
+extern "C" int ffs_get_strong_u8(ffs_ctx* c, int slot, uint8_t* out) {
+    if (!slots_ok(c, slot, 1) || !out) return FFS_ERR_ARG;
+    return get_u8_plane(c, c->d_strong + (size_t)slot * c->bits_stride, out);
+}
+
+extern "C" int ffs_get_extended_stage_u8(ffs_ctx* c, int slot, int stage, uint8_t* out) {
+    if (!slots_ok(c, slot, 1) || !out || (stage != 1 && stage != 2) || !c->d_ext1) return FFS_ERR_ARG;
+    return get_u8_plane(c, (stage == 1 ? c->d_ext1 : c->d_ext2) + (size_t)slot * c->bits_stride, out);
+}

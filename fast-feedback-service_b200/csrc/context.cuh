@@ -1,0 +1,94 @@
+// context.cuh -- the ffs_ctx object behind the C ABI: device buffers, TMA descriptors,
+// streams, the pinned ring of the streaming API.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/ffs_b200.h"
+
+namespace ffsb {
+
+constexpr int kMaxDim = 8192;  // queue entries pack col/row into 13 bits each
+
+inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Per-spot accumulator written by the reduction kernel (see cc.cuh).
+struct SpotAcc;
+
+struct StreamSlot {
+    cudaEvent_t done = nullptr;  // recorded after the slot's result D2H
+    uint64_t frame_id = 0;
+    int state = 0;               // 0 free, 1 acquired (host filling), 2 in flight
+    int stream = 0;
+};
+
+}  // namespace ffsb
+
+struct ffs_ctx {
+    ffs_params p{};
+    int sm_count = 0;
+    std::string err;
+    std::atomic<uint64_t> launches{0};
+
+    // geometry
+    size_t pitch = 0;          // bytes per device image row (multiple of 128)
+    size_t frame_stride = 0;   // bytes per device frame
+    size_t bits_pitch = 0;     // bytes per row of a 1-bit plane (multiple of 16)
+    size_t bits_stride = 0;    // bytes per 1-bit plane
+    int eff_min_count = 2;
+
+    // device memory
+    uint8_t* d_mask = nullptr;        // dense u8 mask
+    uint8_t* d_valid_bits = nullptr;  // 1-bit validity plane
+    uint8_t* d_frames = nullptr;      // n_slots pitched frames
+    uint8_t* d_strong = nullptr;      // n_slots strong bit-planes
+    uint8_t* d_ext1 = nullptr;        // extended: first-pass dispersion bit-planes
+    uint8_t* d_ext2 = nullptr;        // extended: eroded validity bit-planes
+    unsigned int* d_strong_count = nullptr;  // n_slots
+    unsigned long long* d_valid_count = nullptr;
+    uint64_t valid_count = 0;
+
+    // connected components / spots (cc.cuh), per slot
+    uint32_t cap_strong = 0, cap_spots = 0;
+    uint32_t* d_px_index = nullptr;   // n_slots * cap_strong : linear index of strong pixel
+    uint32_t* d_px_value = nullptr;   // n_slots * cap_strong : raw pixel value
+    uint32_t* d_px_parent = nullptr;  // n_slots * cap_strong : union-find parent (compact id)
+    uint32_t* d_chunk_count = nullptr;  // n_slots * n_chunks
+    int n_chunks = 0;
+    ffsb::SpotAcc* d_acc = nullptr;    // n_slots * cap_strong accumulators (indexed by root id)
+    ffs_spot* d_spots = nullptr;      // n_slots * cap_spots
+    uint32_t* d_frame_counts = nullptr;  // n_slots * 8 counters (see cc.cuh)
+    // pinned mirrors for the streaming API
+    uint32_t* h_frame_counts = nullptr;  // n_slots * 8
+    ffs_spot* h_spots = nullptr;         // n_slots * cap_spots
+    uint8_t* h_frames = nullptr;         // n_slots dense pinned frames
+
+    // TMA descriptors
+    CUtensorMap tm_img{};     // 3D: x, y, slot
+    CUtensorMap tm_valid{};   // 2D validity bytes
+    CUtensorMap tm_valid2{};  // 3D eroded validity (extended second pass): x, y, slot
+    bool have_tm = false;
+
+    // streams
+    cudaStream_t stream = nullptr;  // default work stream of the slot API
+    std::vector<cudaStream_t> streams;  // streaming API
+    std::vector<ffsb::StreamSlot> slots;
+    std::deque<int> inflight;  // submitted slots, oldest first
+    std::mutex mu;
+    std::condition_variable cv;
+    int next_stream = 0;
+
+    // sweep (3D) recording
+    bool sweep_on = false;
+    std::vector<uint64_t> sweep_ids;
+    std::vector<std::vector<uint32_t>> sweep_index;  // per frame strong-pixel linear indices
+    std::vector<std::vector<uint32_t>> sweep_value;
+};

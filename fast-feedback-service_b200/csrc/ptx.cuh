@@ -5,7 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-namespace ffs {
+namespace ffsb {
 namespace ptx {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -84,4 +84,4 @@ __device__ __forceinline__ uint4 lds128(const void* p) {
 }
 
 }  // namespace ptx
-}  // namespace ffs
+}  // namespace ffsb

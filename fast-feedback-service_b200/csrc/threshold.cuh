@@ -25,15 +25,16 @@
 #pragma once
 #include "ptx.cuh"
 
-namespace ffs {
+namespace ffsb {
 
 struct ThreshArgs {
     int width, height;
     int n_frames;
+    int slot0;        // first device slot of the batch (TMA z coordinate offset)
     int tile_rows;    // output rows per warp task
     int n_strips;     // ceil(width / OUT_COLS)
     int n_row_tiles;  // ceil(height / tile_rows)
-    const uint8_t* image;  // first frame of the batch, pitched
+    const uint8_t* image;  // slot 0 of the device frame ring, pitched
     size_t pitch;          // bytes per image row
     size_t frame_stride;   // bytes per frame
     const uint8_t* valid_bits;  // 1 bit per pixel, little-endian within a byte
@@ -56,7 +57,9 @@ struct ThreshGeo {
     static constexpr int LOAD_COLS = 32 * PPL;
     static constexpr int OUT_COLS = (32 - 2 * HL) * PPL;
     static constexpr int VPAD = (8 - (HL * PPL) % 8) % 8; // validity tile starts VPAD px earlier
-    static constexpr int VROW_BYTES = ((VPAD + LOAD_COLS + 7) / 8 + 15) / 16 * 16;
+    // TMA box starts must be 16-byte aligned in global memory (measured: a misaligned start
+    // raises 'illegal instruction'), so the validity box starts up to 15 bytes early.
+    static constexpr int VROW_BYTES = ((VPAD + LOAD_COLS + 7) / 8 + 15 + 15) / 16 * 16;
     static constexpr int IMG_STAGE_BYTES = KS * LOAD_COLS * (int)sizeof(PixelT);
     static constexpr int VALID_STAGE_BYTES = (KS * VROW_BYTES + 127) / 128 * 128;
     static constexpr int STAGE_BYTES = IMG_STAGE_BYTES + VALID_STAGE_BYTES;
@@ -67,7 +70,7 @@ struct ThreshGeo {
     static_assert(OUT_COLS % 8 == 0, "strips must start on a validity byte");
     static_assert(IMG_STAGE_BYTES % 128 == 0, "TMA destination alignment");
     static_assert(LOAD_COLS <= 256, "TMA box limit");
-    static constexpr int smem_per_warp(int stages) {
+    __host__ __device__ static constexpr int smem_per_warp(int stages) {
         return stages * STAGE_BYTES + QUEUE_BYTES + 128 /* mbarriers + queue counter */;
     }
 };
@@ -79,6 +82,8 @@ template <typename PixelT, int KH>
 __device__ __forceinline__ bool resolve_dispersion(const ThreshArgs& a, const uint8_t* frame,
                                                    int col, int row, uint32_t m, uint32_t x,
                                                    uint32_t v) {
+    if (sizeof(PixelT) == 4)  // the queue drops values >= 2^24: take the raw centre pixel
+        v = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
     const double md = (double)m, xd = (double)x, vd = (double)v;
     if (!((int)m >= a.min_count && vd > a.threshold)) return false;
     // double b = m * src[k] - x;   double d = nsig_s_ * std::sqrt(x * m);
@@ -155,9 +160,11 @@ __global__ void __launch_bounds__(WARPS * 32)
     if (task >= n_tasks) return;  // whole warp leaves; warps never synchronise with each other
     const int strip = (int)(task % a.n_strips);
     const int rt = (int)((task / a.n_strips) % a.n_row_tiles);
-    const int z = (int)(task / ((long long)a.n_strips * a.n_row_tiles));
+    const int z = a.slot0 + (int)(task / ((long long)a.n_strips * a.n_row_tiles));
 
-    uint8_t* wsm = smem_raw + (size_t)warp * G::smem_per_warp(STAGES);
+    // TMA destinations need 128-byte alignment: align the dynamic window ourselves
+    uint8_t* smem_al = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
+    uint8_t* wsm = smem_al + (size_t)warp * G::smem_per_warp(STAGES);
     uint8_t* stage_base = wsm;
     uint32_t* queue = reinterpret_cast<uint32_t*>(wsm + STAGES * G::STAGE_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(wsm + STAGES * G::STAGE_BYTES + G::QUEUE_BYTES);
@@ -169,7 +176,9 @@ __global__ void __launch_bounds__(WARPS * 32)
     const int n_groups = (n_load_rows + KS - 1) / KS;
     const int x0 = strip * G::OUT_COLS - G::HL * PPL;      // first loaded column (may be < 0)
     const int y_first = r0 - KH;                           // first loaded row   (may be < 0)
-    const int vbyte0 = (x0 - G::VPAD) >> 3;                // arithmetic shift: x0-VPAD is a multiple of 8
+    const int vbyte_first = (x0 - G::VPAD) >> 3;           // arithmetic shift: x0-VPAD is a multiple of 8
+    const int vbyte0 = vbyte_first & ~15;                  // 16-byte aligned TMA start (may be < 0)
+    const int voff = vbyte_first - vbyte0;
 
     if (lane == 0) {
         for (int s = 0; s < STAGES; ++s) ptx::mbar_init(bars + s, 1);
@@ -225,7 +234,7 @@ __global__ void __launch_bounds__(WARPS * 32)
             uint32_t mb;
             {
                 const int bitoff = G::VPAD + lane * PPL;
-                mb = sval[u * G::VROW_BYTES + (bitoff >> 3)];
+                mb = sval[u * G::VROW_BYTES + voff + (bitoff >> 3)];
                 mb = (mb >> (bitoff & 7)) & ((1u << PPL) - 1u);
             }
             uint32_t w[PPL];
@@ -268,7 +277,7 @@ __global__ void __launch_bounds__(WARPS * 32)
             // ---- test the centre row of the window that is now complete -----------------
             const int out_row = r0 + i - 2 * KH;
             if (i >= 2 * KH && out_row < row_end) {  // warp-uniform
-                constexpr int cs = (u + KS - KH) % KS;  // ring slot of the centre row
+                const int cs = (u + KS - KH) % KS;  // ring slot of the centre row
                 uint32_t cb = 0;                        // candidate bits of this lane
                 uint32_t Hx[PPL];
                 uint32_t Hm[PPL];
@@ -399,4 +408,4 @@ __global__ void __launch_bounds__(WARPS * 32)
     if (qn > 0) drain32<PixelT, KH>(a, z, queue, 0, qn, lane);
 }
 
-}  // namespace ffs
+}  // namespace ffsb
