@@ -1,7 +1,8 @@
 // api_core.inl -- lifetime, mask, slot upload, threshold launch, parity hooks.
 
-static constexpr int kThreshStages = 3;
-static constexpr int kThreshWarps = 4;
+static constexpr int kThreshStages = 3;  // TMA stages per warp
+static constexpr int kThreshSR = 4;      // rows per stage
+static constexpr int kThreshWarps = 4;   // warps (independent tasks) per CTA
 
 extern "C" void ffs_default_params(ffs_params* p) {
     if (!p) return;
@@ -83,7 +84,10 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     FFS_CK(c, cudaMalloc(&c->d_valid_bits, c->bits_stride));
     FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
-    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S));
+    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 2));
+    c->d_cand_count = c->d_strong_count + S;
+    c->cand_cap = env_int("FFS_CAND_CAP", (int)std::max<size_t>(px / 8, 4096));
+    FFS_CK(c, cudaMalloc(&c->d_cand, sizeof(uint32_t) * (size_t)c->cand_cap * S));
     FFS_CK(c, cudaMalloc(&c->d_valid_count, sizeof(unsigned long long)));
     FFS_CK(c, cudaMemset(c->d_frames, 0, c->frame_stride * S));
     FFS_CK(c, cudaMemset(c->d_strong, 0, c->bits_stride * S));
@@ -105,16 +109,16 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
         const bool p16 = p.bytes_per_pixel == 2;
         cuuint64_t dims[3] = {p.width, p.height, (cuuint64_t)S};
         cuuint64_t strides[2] = {c->pitch, c->frame_stride};
-        cuuint32_t box[3] = {p16 ? 256u : 128u, (cuuint32_t)(2 * p.kernel_half + 1), 1};
+        cuuint32_t box[3] = {p16 ? 256u : 128u, (cuuint32_t)kThreshSR, 1};
         rc = make_tensor_map(c, &c->tm_img, p16 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32,
                              3, c->d_frames, dims, strides, box);
         if (rc) return rc;
-        cuuint64_t vdims[2] = {(cuuint64_t)(p.width + 7) / 8, p.height};
-        cuuint64_t vstrides[1] = {c->bits_pitch};
-        cuuint32_t vbox[2] = {p16 ? (cuuint32_t)ThreshGeo<uint16_t, 3, 8>::VROW_BYTES
-                                  : (cuuint32_t)ThreshGeo<uint32_t, 3, 4>::VROW_BYTES,
-                              (cuuint32_t)(2 * p.kernel_half + 1)};
-        rc = make_tensor_map(c, &c->tm_valid, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_valid_bits,
+        cuuint64_t vdims[3] = {(cuuint64_t)(p.width + 7) / 8, p.height, 1};
+        cuuint64_t vstrides[2] = {c->bits_pitch, c->bits_stride};
+        cuuint32_t vbox[3] = {p16 ? (cuuint32_t)ThreshGeo<uint16_t, 3, 8, kThreshSR>::VROW_BYTES
+                                  : (cuuint32_t)ThreshGeo<uint32_t, 3, 4, kThreshSR>::VROW_BYTES,
+                              (cuuint32_t)kThreshSR, 1};
+        rc = make_tensor_map(c, &c->tm_valid, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, c->d_valid_bits,
                              vdims, vstrides, vbox);
         if (rc) return rc;
         c->have_tm = true;
@@ -163,6 +167,7 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_ext1);
     cudaFree(c->d_ext2);
     cudaFree(c->d_strong_count);
+    cudaFree(c->d_cand);
     cudaFree(c->d_valid_count);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -218,9 +223,9 @@ static int pick_tile_rows(const ffs_ctx* c, int n_frames, int out_cols, int ks, 
     if (forced > 0) return forced;
     const long long want = 2LL * c->sm_count * 12;
     const int n_strips = ((int)c->p.width + out_cols - 1) / out_cols;
-    int best = ks * 5 - 2 * kh;
-    for (int groups = 19; groups >= 5; --groups) {
-        const int R = groups * ks - 2 * kh;
+    int best = ks * 8 - 2 * kh;
+    for (int groups = 34; groups >= 8; groups -= 2) {
+        const int R = groups * ks - 2 * kh;  // R + 2*kh a multiple of the stage depth
         const long long tasks = (long long)n_frames * n_strips * (((int)c->p.height + R - 1) / R);
         best = R;
         if (tasks >= want) break;
@@ -228,10 +233,36 @@ static int pick_tile_rows(const ffs_ctx* c, int n_frames, int out_cols, int ks, 
     return best;
 }
 
+static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
+    a.width = (int)c->p.width;
+    a.height = (int)c->p.height;
+    a.n_frames = n;
+    a.slot0 = first_slot;
+    a.image = c->d_frames;
+    a.pitch = c->pitch;
+    a.frame_stride = c->frame_stride;
+    a.valid_bits = c->d_valid_bits;
+    a.valid_pitch = c->bits_pitch;
+    a.valid_frame_stride = 0;
+    a.strong_bits = reinterpret_cast<uint32_t*>(c->d_strong);
+    a.strong_pitch = c->bits_pitch;
+    a.strong_frame_stride = c->bits_stride;
+    a.strong_count = c->d_strong_count;
+    a.cand = c->d_cand;
+    a.cand_count = c->d_cand_count;
+    a.cand_cap = c->cand_cap;
+    a.force_brute = env_int("FFS_FORCE_BRUTE", 0);
+    a.nsig_b = c->p.nsig_b;
+    a.nsig_s = c->p.nsig_s;
+    a.threshold = c->p.threshold;
+    a.min_count = c->eff_min_count;
+    a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
+}
+
 template <typename PixelT, int PPL>
 static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
-    using G = ThreshGeo<PixelT, 3, PPL>;
-    auto kern = dispersion_kernel<PixelT, 3, PPL, kThreshStages, kThreshWarps>;
+    using G = ThreshGeo<PixelT, 3, PPL, kThreshSR>;
+    auto kern = prefilter_kernel<PixelT, 3, PPL, kThreshSR, kThreshStages, kThreshWarps>;
     const int smem = kThreshWarps * G::smem_per_warp(kThreshStages) + 128;
     static bool attr_done[64] = {};
     if (!attr_done[c->p.device & 63]) {
@@ -239,30 +270,19 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
         attr_done[c->p.device & 63] = true;
     }
     ThreshArgs a{};
-    a.width = (int)c->p.width;
-    a.height = (int)c->p.height;
-    a.n_frames = n;
-    a.slot0 = first_slot;
-    a.tile_rows = pick_tile_rows(c, n, G::OUT_COLS, G::KS, 3);
+    fill_thresh_args(c, a, first_slot, n);
+    a.tile_rows = pick_tile_rows(c, n, G::OUT_COLS, kThreshSR, 3);
     a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
     a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
-    a.image = c->d_frames;
-    a.pitch = c->pitch;
-    a.frame_stride = c->frame_stride;
-    a.valid_bits = c->d_valid_bits;
-    a.valid_pitch = c->bits_pitch;
-    a.strong_bits = reinterpret_cast<uint32_t*>(c->d_strong);
-    a.strong_pitch = c->bits_pitch;
-    a.strong_frame_stride = c->bits_stride;
-    a.strong_count = c->d_strong_count;
-    a.nsig_b = c->p.nsig_b;
-    a.nsig_s = c->p.nsig_s;
-    a.threshold = c->p.threshold;
-    a.min_count = c->eff_min_count;
-    a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
-    const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
-    const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
-    kern<<<grid, kThreshWarps * 32, smem, st>>>(c->tm_img, c->tm_valid, a);
+    if (!a.force_brute) {
+        const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
+        const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
+        kern<<<grid, kThreshWarps * 32, smem, st>>>(c->tm_img, c->tm_valid, a);
+        c->launches++;
+        FFS_CK(c, cudaGetLastError());
+    }
+    dim3 rgrid((unsigned)(c->sm_count * 4), (unsigned)n);
+    resolve_kernel<PixelT, 3, false><<<rgrid, 256, 0, st>>>(a);
     c->launches++;
     FFS_CK(c, cudaGetLastError());
     return FFS_OK;
@@ -272,6 +292,7 @@ static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     FFS_CK(c, cudaMemsetAsync(c->d_strong + (size_t)first_slot * c->bits_stride, 0,
                               c->bits_stride * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_strong_count + first_slot, 0, sizeof(unsigned) * n, st));
+    FFS_CK(c, cudaMemsetAsync(c->d_cand_count + first_slot, 0, sizeof(unsigned) * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
     if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
     return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);

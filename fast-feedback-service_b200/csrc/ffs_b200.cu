@@ -6,6 +6,7 @@
 #include "extended.cuh"
 #include "cc.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>

@@ -98,3 +98,15 @@ def test_batch_slots_independent():
         sf.threshold(1, 2)
         for i in range(5):
             assert np.array_equal(sf.strong_mask(i), oracle.dispersion(frames[i], mask)), i
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+def test_candidate_overflow_and_brute_paths(dtype, monkeypatch):
+    """A full candidate list must fall back to the exact all-pixel resolve, not drop pixels."""
+    img, mask = random_frame(300, 700, dtype, seed=3, lam=3.0, n_spots=30)
+    want = oracle.dispersion(img, mask)
+    monkeypatch.setenv("FFS_CAND_CAP", "16")
+    assert np.array_equal(run_gpu(img, mask), want)
+    monkeypatch.delenv("FFS_CAND_CAP")
+    monkeypatch.setenv("FFS_FORCE_BRUTE", "1")
+    assert np.array_equal(run_gpu(img, mask), want)
