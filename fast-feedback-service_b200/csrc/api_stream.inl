@@ -1,7 +1,137 @@
-static int stream_setup(ffs_ctx*) { return FFS_OK; }
-static void stream_teardown(ffs_ctx*) {}
-extern "C" int ffs_acquire(ffs_ctx*, int*, void**) { return FFS_ERR_STATE; }
-extern "C" int ffs_submit(ffs_ctx*, int, uint64_t) { return FFS_ERR_STATE; }
-extern "C" int ffs_submit_copy(ffs_ctx*, uint64_t, const void*) { return FFS_ERR_STATE; }
-extern "C" int ffs_wait(ffs_ctx*, ffs_frame_result*, ffs_spot*, size_t, size_t*) { return FFS_ERR_STATE; }
-extern "C" int ffs_pending(ffs_ctx*) { return 0; }
+// api_stream.inl -- streaming API: pinned host ring -> multi-stream H2D -> kernels -> small
+// result D2H.  Replaces the reference's per-thread frame loop (spotfinder.cc:725-1092): one
+// pinned frame + one stream + one device frame per ring slot, no full-mask D2H, no host CC.
+
+static constexpr uint32_t kAsyncSpots = 4096;  // spots copied back asynchronously per frame
+
+static int stream_setup(ffs_ctx* c) {
+    const size_t S = c->p.n_slots;
+    const size_t frame_bytes = (size_t)c->p.width * c->p.height * c->p.bytes_per_pixel;
+    const int n_streams = std::max(1, std::min<int>((int)S, env_int("FFS_STREAMS", 4)));
+    FFS_CK(c, cudaHostAlloc(&c->h_frames, frame_bytes * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaHostAlloc(&c->h_frame_counts, sizeof(uint32_t) * CNT_N * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaHostAlloc(&c->h_spots, sizeof(ffs_spot) * kAsyncSpots * S, cudaHostAllocDefault));
+    c->streams.resize(n_streams);
+    for (auto& s : c->streams) FFS_CK(c, cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    c->slots.resize(S);
+    for (size_t i = 0; i < S; ++i) {
+        FFS_CK(c, cudaEventCreateWithFlags(&c->slots[i].done, cudaEventDisableTiming));
+        c->slots[i].stream = (int)(i % n_streams);
+    }
+    return FFS_OK;
+}
+
+static void stream_teardown(ffs_ctx* c) {
+    for (auto& s : c->slots)
+        if (s.done) cudaEventDestroy(s.done);
+    for (auto& s : c->streams)
+        if (s) cudaStreamDestroy(s);
+    cudaFreeHost(c->h_frames);
+    cudaFreeHost(c->h_frame_counts);
+    cudaFreeHost(c->h_spots);
+}
+
+extern "C" int ffs_acquire(ffs_ctx* c, int* slot, void** pinned_pixels) {
+    if (!c || !slot || !pinned_pixels) return FFS_ERR_ARG;
+    std::unique_lock<std::mutex> lk(c->mu);
+    for (;;) {
+        for (size_t i = 0; i < c->slots.size(); ++i) {
+            if (c->slots[i].state == 0) {
+                c->slots[i].state = 1;
+                *slot = (int)i;
+                *pinned_pixels = c->h_frames + i * ((size_t)c->p.width * c->p.height * c->p.bytes_per_pixel);
+                return FFS_OK;
+            }
+        }
+        // every slot is being filled or in flight: wait until ffs_wait frees one
+        bool any_inflight = !c->inflight.empty();
+        if (!any_inflight) {
+            bool any_filling = false;
+            for (auto& s : c->slots) any_filling |= s.state == 1;
+            if (!any_filling) return FFS_ERR_STATE;
+        }
+        c->cv.wait(lk);
+    }
+}
+
+extern "C" int ffs_submit(ffs_ctx* c, int slot, uint64_t frame_id) {
+    if (!slots_ok(c, slot, 1)) return FFS_ERR_ARG;
+    std::unique_lock<std::mutex> lk(c->mu);
+    StreamSlot& s = c->slots[slot];
+    if (s.state != 1) return FFS_ERR_STATE;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    cudaStream_t st = c->streams[s.stream];
+    const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+    FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
+                                c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
+                                cudaMemcpyHostToDevice, st));
+    int rc = threshold_impl(c, slot, 1, st);
+    if (rc == FFS_OK) rc = cc_impl(c, slot, 1, st);
+    if (rc) return rc;
+    FFS_CK(c, cudaMemcpyAsync(c->h_frame_counts + (size_t)slot * CNT_N, c->d_frame_counts + (size_t)slot * CNT_N,
+                              sizeof(uint32_t) * CNT_N, cudaMemcpyDeviceToHost, st));
+    FFS_CK(c, cudaMemcpyAsync(c->h_spots + (size_t)slot * kAsyncSpots, c->d_spots + (size_t)slot * c->cap_spots,
+                              sizeof(ffs_spot) * std::min(kAsyncSpots, c->cap_spots), cudaMemcpyDeviceToHost, st));
+    FFS_CK(c, cudaEventRecord(s.done, st));
+    s.frame_id = frame_id;
+    s.state = 2;
+    c->inflight.push_back(slot);
+    c->cv.notify_all();
+    return FFS_OK;
+}
+
+extern "C" int ffs_submit_copy(ffs_ctx* c, uint64_t frame_id, const void* pixels) {
+    if (!c || !pixels) return FFS_ERR_ARG;
+    int slot = -1;
+    void* dst = nullptr;
+    int rc = ffs_acquire(c, &slot, &dst);
+    if (rc) return rc;
+    memcpy(dst, pixels, (size_t)c->p.width * c->p.height * c->p.bytes_per_pixel);
+    return ffs_submit(c, slot, frame_id);
+}
+
+extern "C" int ffs_pending(ffs_ctx* c) {
+    if (!c) return 0;
+    std::lock_guard<std::mutex> lk(c->mu);
+    return (int)c->inflight.size();
+}
+
+extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, size_t max_spots,
+                        size_t* n_spots) {
+    if (!c) return FFS_ERR_ARG;
+    int slot;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (c->inflight.empty()) return FFS_ERR_STATE;
+        slot = c->inflight.front();
+        c->inflight.pop_front();
+    }
+    StreamSlot& s = c->slots[slot];
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaEventSynchronize(s.done));
+    const uint32_t* cnt = c->h_frame_counts + (size_t)slot * CNT_N;
+    if (result) counts_to_result(cnt, s.frame_id, result);
+    const size_t have = std::min<size_t>(cnt[CNT_COMPONENTS], c->cap_spots);
+    if (n_spots) *n_spots = have;
+    int rc = FFS_OK;
+    if (spots && max_spots) {
+        const size_t k = std::min(have, max_spots);
+        const size_t k_async = std::min<size_t>(k, kAsyncSpots);
+        memcpy(spots, c->h_spots + (size_t)slot * kAsyncSpots, k_async * sizeof(ffs_spot));
+        if (k > k_async) {  // rare: more spots than the async window
+            cudaError_t e = cudaMemcpy(spots + k_async, c->d_spots + (size_t)slot * c->cap_spots + k_async,
+                                       (k - k_async) * sizeof(ffs_spot), cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) {
+                c->err = cudaGetErrorString(e);
+                rc = FFS_ERR_CUDA;
+            }
+        }
+    }
+    if (rc == FFS_OK && c->sweep_on) rc = sweep_record(c, slot, s.frame_id, cnt[CNT_STRONG]);
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        s.state = 0;
+    }
+    c->cv.notify_all();
+    return rc;
+}

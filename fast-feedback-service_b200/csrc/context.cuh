@@ -94,4 +94,5 @@ struct ffs_ctx {
     std::vector<uint64_t> sweep_ids;
     std::vector<std::vector<uint32_t>> sweep_index;  // per frame strong-pixel linear indices
     std::vector<std::vector<uint32_t>> sweep_value;
+    std::vector<uint32_t> sweep_plane[2];  // {index, component rank} of the first / last slice
 };

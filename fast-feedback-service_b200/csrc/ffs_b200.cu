@@ -5,11 +5,13 @@
 #include "threshold.cuh"
 #include "extended.cuh"
 #include "cc.cuh"
+#include "cc3d.cuh"
 
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace ffsb {
 
@@ -81,8 +83,11 @@ static int cc_setup(ffs_ctx* c);
 static void cc_teardown(ffs_ctx* c);
 static int stream_setup(ffs_ctx* c);
 static void stream_teardown(ffs_ctx* c);
+static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_strong);
 
 #include "api_core.inl"
+#include "api_ext.inl"
 #include "api_cc.inl"
 #include "api_stream.inl"
+#include "api_sweep.inl"
 #include "api_shim.inl"

@@ -99,6 +99,7 @@ SYMBOLS = {
     "ffs_wait": (_i, [_vp, C.POINTER(FrameResult), _vp, _sz, C.POINTER(_sz)]),
     "ffs_pending": (_i, [_vp]),
     "ffs_sweep_begin": (_i, [_vp, C.c_uint64]),
+    "ffs_sweep_record_slot": (_i, [_vp, _i, C.c_uint64]),
     "ffs_sweep_finish": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_plane": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_free": (None, [_vp]),

@@ -187,3 +187,63 @@ class Spotfinder:
             else max_peak_centroid_separation
         kept = self._L.ffs_filter_spots(s.ctypes.data, len(s), ms, sep, C.byref(a), C.byref(b))
         return s[:kept].copy(), a.value, b.value
+
+    # -- streaming API (host frames in, per-frame results out) -----------------------------
+    def acquire(self):
+        """(slot, ndarray view of the slot's pinned host frame) -- fill it, then submit()."""
+        slot, ptr = C.c_int(-1), C.c_void_p()
+        self._ck(self._L.ffs_acquire(self._ctx, C.byref(slot), C.byref(ptr)), "ffs_acquire")
+        n = self.height * self.width
+        buf = (C.c_uint8 * (n * self.dtype.itemsize)).from_address(ptr.value)
+        return slot.value, np.frombuffer(buf, dtype=self.dtype).reshape(self.height, self.width)
+
+    def submit(self, slot: int, frame_id: int):
+        self._ck(self._L.ffs_submit(self._ctx, slot, frame_id), "ffs_submit")
+
+    def submit_copy(self, frame_id: int, frame: np.ndarray):
+        f = np.ascontiguousarray(frame, dtype=self.dtype)
+        if f.shape != (self.height, self.width):
+            raise ValueError("frame shape must be (height, width)")
+        self._ck(self._L.ffs_submit_copy(self._ctx, frame_id, f.ctypes.data), "ffs_submit_copy")
+
+    @property
+    def pending(self) -> int:
+        return self._L.ffs_pending(self._ctx)
+
+    def wait(self, max_spots: int = 4096):
+        """Oldest submitted frame: (FrameResult, spots[:min(n, max_spots)])."""
+        res, n = FrameResult(), C.c_size_t(0)
+        spots = np.zeros(max(max_spots, 1), SPOT_DTYPE)
+        self._ck(self._L.ffs_wait(self._ctx, C.byref(res), spots.ctypes.data, max_spots, C.byref(n)), "ffs_wait")
+        return res, spots[:min(n.value, max_spots)]
+
+    # -- rotation sweeps: 3D connected components --------------------------------------------
+    def sweep_begin(self, max_frames: int = 0):
+        self._ck(self._L.ffs_sweep_begin(self._ctx, max_frames), "ffs_sweep_begin")
+
+    def sweep_record_slot(self, slot: int, frame_id: int):
+        self._ck(self._L.ffs_sweep_record_slot(self._ctx, slot, frame_id), "ffs_sweep_record_slot")
+
+    def sweep_finish(self) -> np.ndarray:
+        """All 3D components of the recorded frames, unfiltered, canonical order
+        (find_3d_components before filter_reflections)."""
+        ptr, n = C.c_void_p(), C.c_size_t(0)
+        self._ck(self._L.ffs_sweep_finish(self._ctx, C.byref(ptr), C.byref(n)), "ffs_sweep_finish")
+        if not n.value:
+            return np.zeros(0, SPOT_DTYPE)
+        buf = (C.c_uint8 * (n.value * SPOT_DTYPE.itemsize)).from_address(ptr.value)
+        out = np.frombuffer(buf, dtype=SPOT_DTYPE).copy()
+        self._L.ffs_free(ptr)
+        return out
+
+    def sweep_export_plane(self, which: int) -> np.ndarray:
+        """(n, 2) uint32 {linear index, component rank} of the first (0) / last (1) slice."""
+        ptr, n = C.c_void_p(), C.c_size_t(0)
+        self._ck(self._L.ffs_sweep_export_plane(self._ctx, which, C.byref(ptr), C.byref(n)),
+                 "ffs_sweep_export_plane")
+        if not n.value:
+            return np.zeros((0, 2), np.uint32)
+        buf = (C.c_uint32 * (2 * n.value)).from_address(ptr.value)
+        out = np.frombuffer(buf, dtype=np.uint32).reshape(-1, 2).copy()
+        self._L.ffs_free(ptr)
+        return out

@@ -182,6 +182,9 @@ int ffs_pending(ffs_ctx *ctx);
  * in ascending frame_id order (cc:409,441), and returns all components UNFILTERED in
  * canonical order.  The caller frees *spots with ffs_free. */
 int ffs_sweep_begin(ffs_ctx *ctx, uint64_t max_frames);
+/* Slot-API counterpart of the recording ffs_wait does: add the last ffs_process result of
+ * `slot` to the sweep as frame `frame_id`. */
+int ffs_sweep_record_slot(ffs_ctx *ctx, int slot, uint64_t frame_id);
 int ffs_sweep_finish(ffs_ctx *ctx, ffs_spot **spots, size_t *n_spots);
 /* Boundary exchange for slab-sharded sweeps (one slab of consecutive frames per GPU).
  * ffs_sweep_export_plane packs the strong pixels of the slab's first (which=0) or last
