@@ -169,8 +169,35 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_strong_count);
     cudaFree(c->d_cand);
     cudaFree(c->d_valid_count);
+    for (auto& ev : c->prof_events) {
+        cudaEventDestroy(ev.first);
+        cudaEventDestroy(ev.second);
+    }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+extern "C" int ffs_profile_enable(ffs_ctx* c, int on) {
+    if (!c) return FFS_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->prof_on = on != 0;
+    return FFS_OK;
+}
+
+extern "C" int ffs_profile_read(ffs_ctx* c, double* total_ms, uint64_t* n_launches) {
+    if (!c) return FFS_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    double tot = 0;
+    for (size_t i = 0; i < c->prof_used; ++i) {
+        float ms = 0;
+        FFS_CK(c, cudaEventSynchronize(c->prof_events[i].second));
+        FFS_CK(c, cudaEventElapsedTime(&ms, c->prof_events[i].first, c->prof_events[i].second));
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (n_launches) *n_launches = c->prof_used;
+    c->prof_used = 0;
+    return FFS_OK;
 }
 
 extern "C" uint64_t ffs_kernel_launches(const ffs_ctx* c) { return c ? c->launches.load() : 0; }
@@ -277,7 +304,22 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
     if (!a.force_brute) {
         const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
         const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (c->prof_on) {
+            std::lock_guard<std::mutex> lk(c->mu);
+            if (c->prof_used == c->prof_events.size()) {
+                std::pair<cudaEvent_t, cudaEvent_t> ev;
+                cudaEventCreate(&ev.first);
+                cudaEventCreate(&ev.second);
+                c->prof_events.push_back(ev);
+            }
+            e0 = c->prof_events[c->prof_used].first;
+            e1 = c->prof_events[c->prof_used].second;
+            c->prof_used++;
+        }
+        if (e0) cudaEventRecord(e0, st);
         kern<<<grid, kThreshWarps * 32, smem, st>>>(c->tm_img, c->tm_valid, a);
+        if (e1) cudaEventRecord(e1, st);
         c->launches++;
         FFS_CK(c, cudaGetLastError());
     }

@@ -89,6 +89,11 @@ struct ffs_ctx {
     std::condition_variable cv;
     int next_stream = 0;
 
+    // per-kernel profiling (ffs_profile_*)
+    bool prof_on = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    size_t prof_used = 0;
+
     // sweep (3D) recording
     bool sweep_on = false;
     std::vector<uint64_t> sweep_ids;

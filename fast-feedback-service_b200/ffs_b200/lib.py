@@ -105,6 +105,8 @@ SYMBOLS = {
     "ffs_free": (None, [_vp]),
     "ffs_filter_spots": (_sz, [_vp, _sz, C.c_uint32, C.c_float, C.POINTER(_sz), C.POINTER(_sz)]),
     "ffs_kernel_launches": (C.c_uint64, [_vp]),
+    "ffs_profile_enable": (_i, [_vp, _i]),
+    "ffs_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "ffs_frame_pitch": (_sz, [_vp]),
     "ffs_frame_bytes_device": (_sz, [_vp]),
     "spotfinder_create": (_vp, [_sz, _sz]),

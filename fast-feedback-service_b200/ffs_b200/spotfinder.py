@@ -247,3 +247,13 @@ class Spotfinder:
         out = np.frombuffer(buf, dtype=np.uint32).reshape(-1, 2).copy()
         self._L.ffs_free(ptr)
         return out
+
+    # -- instrumentation -----------------------------------------------------------------------
+    def profile_enable(self, on: bool = True):
+        self._ck(self._L.ffs_profile_enable(self._ctx, int(on)), "ffs_profile_enable")
+
+    def profile_read(self):
+        """(total ms, launches) of the bracketed dominant kernel since the last read."""
+        ms, n = C.c_double(0), C.c_uint64(0)
+        self._ck(self._L.ffs_profile_read(self._ctx, C.byref(ms), C.byref(n)), "ffs_profile_read")
+        return ms.value, n.value
