@@ -84,8 +84,10 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     FFS_CK(c, cudaMalloc(&c->d_valid_bits, c->bits_stride));
     FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
-    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 2));
+    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 3));
     c->d_cand_count = c->d_strong_count + S;
+    c->d_ext_count = c->d_strong_count + 2 * S;
+    FFS_CK(c, cudaMemset(c->d_strong_count, 0, sizeof(unsigned) * S * 3));
     c->cand_cap = env_int("FFS_CAND_CAP", (int)std::max<size_t>(px / 8, 4096));
     FFS_CK(c, cudaMalloc(&c->d_cand, sizeof(uint32_t) * (size_t)c->cand_cap * S));
     FFS_CK(c, cudaMalloc(&c->d_valid_count, sizeof(unsigned long long)));

@@ -54,6 +54,7 @@ struct ffs_ctx {
     uint8_t* d_ext2 = nullptr;        // extended: eroded validity bit-planes
     unsigned int* d_strong_count = nullptr;  // n_slots (+ n_slots candidate counters behind)
     unsigned int* d_cand_count = nullptr;    // alias into d_strong_count
+    unsigned int* d_ext_count = nullptr;     // alias: scratch counter of the extended first pass
     uint32_t* d_cand = nullptr;              // n_slots * cand_cap candidate pixels
     unsigned int cand_cap = 0;
     unsigned long long* d_valid_count = nullptr;

@@ -1,3 +1,155 @@
-// extended.cuh -- dispersion_extended kernels (placeholder, filled in below)
+// extended.cuh -- DispersionExtendedThreshold (baseline/spotfinder/baseline.cpp:325-813).
+//
+//   pass 1   compute_dispersion_threshold (:415-475): D = mask && m >= min_count && a > c
+//            -> resolve_kernel<.., EXT_PASS1 = true> over every pixel (exact integer window
+//               gather + fp64 test), strong plane = the ext1 bit-plane.
+//   erosion  erode_dispersion_mask (:552-571): B = mask ? !(D && chebyshev_distance >= 3) : 0.
+//            distance >= 3 to the nearest false pixel == "all of the in-image 5x5
+//            neighbourhood is true", so this is pure bit-plane logic (erode_kernel).  Masked
+//            pixels have D = 0 and therefore erode their neighbours, as in the reference CPU
+//            code (the reference GPU kernel skips them: spotfinder/kernels/erosion.cu:101-105).
+//   pass 2   compute_sat(table, src, B) + compute_final_threshold (:580-645): 11x11 window
+//            over B-valid pixels; strong iff the pixel is in the eroded core (!B), v > threshold
+//            and v >= mean + nsig_s*sqrt(mean).  Only core pixels can be strong and they are
+//            sparse, so erode_kernel emits them as a candidate list and final_kernel gathers
+//            the 11x11 window for those alone -- no second box filter over the frame.
 #pragma once
 #include "threshold.cuh"
+
+namespace ffsb {
+
+struct ErodeArgs {
+    int width, height, n_frames, slot0;
+    int words_per_row;
+    const uint32_t* mask_bits;   // validity plane of the dataset
+    const uint32_t* d_bits;      // pass-1 plane(s) (ext1)
+    uint32_t* b_bits;            // output plane(s) (ext2): valid and not in the core
+    size_t bits_stride;          // bytes per plane
+    uint32_t* cand;              // per slot: core pixels  col | row << 13
+    unsigned int* cand_count;
+    unsigned int cand_cap;
+};
+
+// One thread per 32-bit word of the plane.  grid (blocks, n_frames).
+__global__ void __launch_bounds__(256) erode_kernel(const ErodeArgs a) {
+    const int z = a.slot0 + blockIdx.y;
+    const uint32_t* D = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(a.d_bits) +
+                                                          (size_t)z * a.bits_stride);
+    uint32_t* B = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(a.b_bits) + (size_t)z * a.bits_stride);
+    const int wpr = a.words_per_row;
+    const int n_words = wpr * a.height;
+    const int last_word = (a.width - 1) >> 5;
+    const uint32_t last_valid = (a.width & 31) ? ((1u << (a.width & 31)) - 1u) : 0xffffffffu;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_words; t += gridDim.x * blockDim.x) {
+        const int row = t / wpr, wi = t - row * wpr;
+        uint32_t core = 0xffffffffu;
+        if (wi > last_word) {
+            B[t] = 0;
+            continue;
+        }
+        // out-of-image pixels are ignored by the distance transform: they read as "true"
+        auto word = [&](int r, int w) -> uint32_t {
+            if (r < 0 || r >= a.height || w < 0 || w > last_word) return 0xffffffffu;
+            uint32_t v = D[(size_t)r * wpr + w];
+            if (w == last_word) v |= ~last_valid;
+            return v;
+        };
+#pragma unroll
+        for (int dr = -2; dr <= 2; ++dr) {
+            const int r = row + dr;
+            const uint32_t c = word(r, wi), l = word(r, wi - 1), rt = word(r, wi + 1);
+            // bit i of the result = AND of bits i-2 .. i+2 of the row
+            uint32_t h = c;
+            h &= (c << 1) | (l >> 31);
+            h &= (c << 2) | (l >> 30);
+            h &= (c >> 1) | (rt << 31);
+            h &= (c >> 2) | (rt << 30);
+            core &= h;
+        }
+        const uint32_t m = a.mask_bits[t];
+        const uint32_t valid_cols = wi == last_word ? last_valid : 0xffffffffu;
+        core &= m & valid_cols;  // the centre itself is in D (dr = 0), D implies mask
+        B[t] = m & ~core & valid_cols;
+        // core pixels are the only possible strong pixels of the final pass
+        uint32_t bits = core;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const unsigned slot = atomicAdd(a.cand_count + z, 1u);
+            if (slot < a.cand_cap) a.cand[(size_t)z * a.cand_cap + slot] = (uint32_t)(wi * 32 + b) | ((uint32_t)row << 13);
+        }
+    }
+}
+
+// compute_final_threshold for one pixel (baseline.cpp:630-643).  valid = the B plane of this
+// frame (validity of the second summed-area table), mask = the dataset's validity plane.
+template <typename PixelT, int KH>
+__device__ __forceinline__ bool resolve_final_pixel(const ThreshArgs& a, const uint8_t* frame,
+                                                    const uint8_t* bplane, const uint8_t* mask, int col,
+                                                    int row) {
+    const size_t boff = (size_t)row * a.valid_pitch + (col >> 3);
+    if (!((mask[boff] >> (col & 7)) & 1u)) return false;    // mask[k]
+    if ((bplane[boff] >> (col & 7)) & 1u) return false;     // dispersion_mask = !dst[k]
+    const int x0 = max(col - KH, 0), x1 = min(col + KH, a.width - 1);
+    const int y0 = max(row - KH, 0), y1 = min(row + KH, a.height - 1);
+    uint32_t m = 0;
+    unsigned long long x = 0;
+    for (int yy = y0; yy <= y1; ++yy) {
+        const PixelT* prow = reinterpret_cast<const PixelT*>(frame + (size_t)yy * a.pitch);
+        const uint8_t* vrow = bplane + (size_t)yy * a.valid_pitch;
+        const int byte0 = x0 >> 3;
+        uint32_t bits = vrow[byte0];
+        if ((x1 >> 3) > byte0) bits |= (uint32_t)vrow[byte0 + 1] << 8;
+        if ((x1 >> 3) > byte0 + 1) bits |= (uint32_t)vrow[byte0 + 2] << 16;
+        bits >>= (x0 & 7);
+#pragma unroll
+        for (int k = 0; k < 2 * KH + 1; ++k) {
+            const int xx = x0 + k;
+            if (xx <= x1) {
+                const uint32_t pv = prow[xx];
+                if (((bits >> k) & 1u) && pv < (1u << 24)) {
+                    m += 1;
+                    x += pv;
+                }
+            }
+        }
+    }
+    const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    if (!(vd > a.threshold)) return false;                  // global_mask
+    // double mean = (m >= 2 ? (x / m) : 0);  local_mask = src[k] >= mean + nsig_s_ * sqrt(mean)
+    const double mean = m >= 2 ? __ddiv_rn((double)x, (double)m) : 0.0;
+    return vd >= __dadd_rn(mean, __dmul_rn(a.nsig_s, __dsqrt_rn(mean)));
+}
+
+// grid (blocks, n_frames): one thread per core pixel (or per pixel if the list overflowed)
+template <typename PixelT, int KH>
+__global__ void __launch_bounds__(256) final_kernel(const ThreshArgs a, const uint8_t* mask_bits) {
+    const int z = a.slot0 + blockIdx.y;
+    const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
+    const uint8_t* bplane = a.valid_bits + (size_t)z * a.valid_frame_stride;
+    const unsigned n_cand = a.cand_count[z];
+    const bool brute = a.force_brute || n_cand > a.cand_cap;
+    const long long total = brute ? (long long)a.width * a.height : (long long)n_cand;
+    const uint32_t* list = a.cand + (size_t)z * a.cand_cap;
+    unsigned found = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        int col, row;
+        if (brute) {
+            row = (int)(t / a.width);
+            col = (int)(t % a.width);
+        } else {
+            const uint32_t e = list[t];
+            col = e & 0x1fff;
+            row = e >> 13;
+        }
+        if (resolve_final_pixel<PixelT, KH>(a, frame, bplane, mask_bits, col, row)) {
+            set_strong(a, z, col, row);
+            ++found;
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
+    if ((threadIdx.x & 31) == 0 && found) atomicAdd(a.strong_count + z, found);
+}
+
+}  // namespace ffsb
