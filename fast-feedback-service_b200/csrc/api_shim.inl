@@ -68,3 +68,16 @@ extern "C" uint32_t spotfinder_standard_dispersion(void* context, ffs_image_t* i
 extern "C" uint32_t spotfinder_standard_dispersion32(void* context, ffs_image_t* image, ffs_bool** destination) {
     return shim_dispersion(context, image, destination);
 }
+
+// Host-side ingestion helper shared with the spotfinder executable (cli/bslz4.hpp): decode one
+// bitshuffle-LZ4 HDF5-filter chunk (12-byte header + body) into n dense elements.
+#include "cli/bslz4.hpp"
+extern "C" int ffs_bslz4_decode_chunk(const void* chunk, size_t chunk_bytes, void* out, size_t n_elements,
+                                      size_t elem_size) {
+    if (!chunk || !out || (elem_size != 2 && elem_size != 4)) return FFS_ERR_ARG;
+    static thread_local std::vector<uint8_t> scratch;
+    return bslz4::decompress_chunk(static_cast<const uint8_t*>(chunk), chunk_bytes, out, n_elements, elem_size,
+                                   scratch) == 0
+             ? FFS_OK
+             : FFS_ERR_ARG;
+}

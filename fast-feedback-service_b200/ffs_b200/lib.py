@@ -109,6 +109,7 @@ SYMBOLS = {
     "ffs_profile_read": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "ffs_frame_pitch": (_sz, [_vp]),
     "ffs_frame_bytes_device": (_sz, [_vp]),
+    "ffs_bslz4_decode_chunk": (_i, [_vp, _sz, _vp, _sz, _sz]),
     "spotfinder_create": (_vp, [_sz, _sz]),
     "spotfinder_free": (None, [_vp]),
     "spotfinder_standard_dispersion": (C.c_uint32, [_vp, C.POINTER(ImageT), C.POINTER(_vp)]),

@@ -214,6 +214,13 @@ int ffs_profile_read(ffs_ctx *ctx, double *total_ms, uint64_t *n_launches);
 size_t ffs_frame_pitch(const ffs_ctx *ctx);
 size_t ffs_frame_bytes_device(const ffs_ctx *ctx);
 
+/* ---- ingestion helper ----------------------------------------------------------------------- */
+/* bshuf_decompress_lz4(chunk + 12, out, n, elem_size, 0) as the reference frame loop calls it
+ * (spotfinder/spotfinder.cc:830-834): decode one bitshuffle-LZ4 HDF5-filter chunk (12-byte
+ * header + body) into n dense elements (host memory, e.g. a pinned ffs_acquire slot). */
+int ffs_bslz4_decode_chunk(const void *chunk, size_t chunk_bytes, void *out, size_t n_elements,
+                           size_t elem_size);
+
 /* ---- baseline.h-compatible shim (baseline/spotfinder/baseline.h:9-13) -------------------- */
 /* image_t as h5read/include/h5read.h:34-39 declares it; image_t_type is uint16_t here
  * (uint32_t when the caller was built with PIXEL_DATA_32BIT: use the *32 entry points). */

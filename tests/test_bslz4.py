@@ -1,0 +1,47 @@
+"""CPU-only: the bitshuffle-LZ4 chunk decoder (host ingestion, csrc/cli/bslz4.hpp) round-trips
+the test-side encoder, including ragged tails and corrupt input."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from bslz4_ref import compress_chunk
+from ffs_b200 import lib
+
+
+def decode(chunk: bytes, n: int, dtype):
+    out = np.zeros(n, dtype)
+    rc = lib.load().ffs_bslz4_decode_chunk(chunk, len(chunk), out.ctypes.data, n, out.dtype.itemsize)
+    return rc, out
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+@pytest.mark.parametrize("n", [8, 9, 4096, 4097, 5000, 8191, 12345, 70 * 90])
+def test_roundtrip(n, dtype):
+    rng = np.random.default_rng(n)
+    a = rng.poisson(3.0, n).astype(dtype)
+    a[rng.integers(0, n, max(1, n // 50))] = np.iinfo(dtype).max  # gap pixels
+    rc, out = decode(compress_chunk(a), n, dtype)
+    assert rc == 0 and np.array_equal(out, a)
+
+
+def test_incompressible_and_constant():
+    rng = np.random.default_rng(1)
+    a = rng.integers(0, 65536, 10000).astype(np.uint16)
+    rc, out = decode(compress_chunk(a), a.size, np.uint16)
+    assert rc == 0 and np.array_equal(out, a)
+    z = np.zeros(20000, np.uint32)
+    chunk = compress_chunk(z)
+    assert len(chunk) < z.nbytes // 20
+    rc, out = decode(chunk, z.size, np.uint32)
+    assert rc == 0 and not out.any()
+
+
+def test_corrupt_input_is_rejected():
+    a = np.arange(5000, dtype=np.uint16)
+    chunk = compress_chunk(a)
+    assert decode(chunk[:-7], a.size, np.uint16)[0] != 0       # truncated
+    assert decode(chunk, a.size + 8, np.uint16)[0] != 0        # wrong element count
+    bad = bytearray(chunk)
+    bad[12:16] = b"\xff\xff\xff\xff"                           # absurd block length
+    assert decode(bytes(bad), a.size, np.uint16)[0] != 0
