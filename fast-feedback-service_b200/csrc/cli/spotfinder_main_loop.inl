@@ -1,0 +1,186 @@
+    // ---- continuation of main(): context, frame loop, results (spotfinder.cc:606-1331) ----------
+    ffs_params p;
+    ffs_default_params(&p);
+    p.width = width;
+    p.height = height;
+    p.bytes_per_pixel = sizeof(pixel_t);
+    p.algorithm = algo == "dispersion" ? FFS_ALGO_DISPERSION : FFS_ALGO_DISPERSION_EXTENDED;
+    p.min_spot_size = args.min_spot_size;
+    p.min_spot_size_3d = args.min_spot_size_3d;
+    p.max_peak_centroid_separation = args.max_peak_centroid_separation;
+    p.device = args.device;
+    p.n_slots = (int32_t)std::min<uint32_t>(std::max<uint32_t>(args.threads + 2, 6), 24);
+    ffs_ctx* ctx = nullptr;
+    if (int rc = ffs_create(&p, reader.get_mask().data(), &ctx)) {
+        printf("Error: could not initialise the GPU spotfinder (%d): %s\n", rc, ffs_last_error(nullptr));
+        return 1;
+    }
+    printf("Mask has %llu valid pixels of %u\n", (unsigned long long)ffs_mask_valid_count(ctx), width * height);
+    if (args.dmin > 0 || args.dmax > 0) {  // apply_resolution_filtering, spotfinder.cc:110-137,650-652
+        if (ffs_apply_resolution_mask(ctx, wavelength, det.distance, det.beam_center_x, det.beam_center_y,
+                                      det.pixel_size_x, det.pixel_size_y, args.dmin, args.dmax)) {
+            printf("Error: resolution mask failed: %s\n", ffs_last_error(ctx));
+            return 1;
+        }
+        printf("Resolution mask applied: %llu valid pixels remain\n", (unsigned long long)ffs_mask_valid_count(ctx));
+    }
+    if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain\n");
+    if (args.save_h5) printf("Note: results_ffs.h5 cannot be written by this build (libhdf5 unavailable)\n");
+    std::unique_ptr<PipeHandler> pipe;
+    if (args.pipe_fd != -1) pipe = std::make_unique<PipeHandler>(args.pipe_fd);
+    if (rotation) ffs_sweep_begin(ctx, num_images);
+
+    const size_t px = (size_t)width * height;
+    std::atomic<uint32_t> next_image{0}, submitted{0}, completed{0};
+    std::atomic<int> workers_alive{(int)args.threads};
+    std::vector<int> thread_of(num_images, 0);
+    std::mutex wait_mutex;
+    double time_waiting_for_images = 0;
+    auto last_image_received = clk::now();
+    const auto all_images_start = clk::now();
+    printf("Finding spots in %u images (%u x %u) with %u threads\n", num_images, width, height, args.threads);
+
+    auto worker = [&](int thread_id) {
+        std::vector<uint8_t> chunk, scratch;
+        while (!g_stop) {
+            const uint32_t image_num = next_image.fetch_add(1);
+            if (image_num >= num_images) break;
+            const size_t offset_image_num = image_num + args.start_index;
+            {   // availability poll every 100 ms, abort after `timeout` s without a new image (:770-787)
+                const auto wait_start = clk::now();
+                while (!reader.is_image_available(offset_image_num) && !g_stop) {
+                    std::lock_guard<std::mutex> lk(wait_mutex);
+                    if (seconds_since(last_image_received) > args.timeout) {
+                        printf("Timeout waiting for image %zu\n", offset_image_num);
+                        g_stop = true;
+                        break;
+                    }
+                    std::this_thread::sleep_for(100ms);
+                }
+                if (g_stop) break;
+                std::lock_guard<std::mutex> lk(wait_mutex);
+                last_image_received = clk::now();
+                time_waiting_for_images += seconds_since(wait_start);
+            }
+            for (;;) {  // zero-length chunk = writer not finished: sleep and retry (:805-821)
+                if (!reader.get_raw_chunk(offset_image_num, chunk) || chunk.empty()) {
+                    printf("Race Condition?!?? Got buffer size 0 for image %u. Sleeping.\n", image_num);
+                    std::this_thread::sleep_for(100ms);
+                    if (g_stop) break;
+                    continue;
+                }
+                break;
+            }
+            if (g_stop) break;
+            int slot = -1;
+            void* pinned = nullptr;
+            if (ffs_acquire(ctx, &slot, &pinned) != FFS_OK) break;
+            // decompress straight into the pinned ring slot (no intermediate host copy)
+            if (bslz4::decompress_chunk(chunk.data(), chunk.size(), pinned, px, sizeof(pixel_t), scratch) != 0) {
+                printf("Error: could not decompress image %zu\n", offset_image_num);
+                g_stop = true;
+                memset(pinned, 0, px * sizeof(pixel_t));
+            }
+            thread_of[image_num] = thread_id;
+            if (ffs_submit(ctx, slot, image_num) != FFS_OK) {
+                printf("Error: submit failed: %s\n", ffs_last_error(ctx));
+                g_stop = true;
+                break;
+            }
+            submitted++;
+        }
+        workers_alive--;
+    };
+
+    auto collector = [&]() {
+        std::vector<ffs_spot> spots(65536);
+        for (;;) {
+            ffs_frame_result r;
+            size_t n = 0;
+            const int rc = ffs_wait(ctx, &r, spots.data(), spots.size(), &n);
+            if (rc == FFS_ERR_STATE) {
+                if (workers_alive == 0 && completed >= submitted) break;
+                std::this_thread::sleep_for(200us);
+                continue;
+            }
+            if (rc != FFS_OK) {
+                printf("Error: %s\n", ffs_last_error(ctx));
+                g_stop = true;
+                continue;
+            }
+            if (r.status != 0) printf("Warning: image %llu exceeded a spot-list capacity; results truncated\n", (unsigned long long)r.frame_id);
+            if (n > spots.size()) n = spots.size();
+            const uint32_t image_num = (uint32_t)r.frame_id;
+            // ConnectedComponents::generate_boxes log lines (connected_components.cc:119,133)
+            printf("Extracted %u spots\n", r.n_components);
+            if (args.min_spot_size > 0)
+                printf("Removed %u spots with size < %u pixels\n", r.n_components - r.n_spots_total, args.min_spot_size);
+            std::string centers;
+            if (!rotation && (args.save_h5 || args.output_for_index)) {  // find_2d_components (:238-266)
+                const size_t kept = ffs_filter_spots(spots.data(), n, args.min_spot_size, args.max_peak_centroid_separation,
+                                                     nullptr, nullptr);
+                if (r.n_spots_total > kept)
+                    printf("Filtered %zu spots with peak-centroid distance > %s\n", (size_t)r.n_spots_total - kept,
+                           shortest(args.max_peak_centroid_separation).c_str());
+                for (size_t i = 0; i < kept; ++i) {
+                    if (i) centers += ",";
+                    centers += jsonmini::number(spots[i].com_x) + "," + jsonmini::number(spots[i].com_y) + "," +
+                               jsonmini::number(spots[i].com_z);
+                }
+            }
+            if (pipe) {  // keys in sorted order, as nlohmann::json dumps them (spotfinder.cc:997-1008)
+                std::string js = "{\"file\":" + jsonmini::escape(file) + ",\"file-number\":" + std::to_string(image_num) +
+                                 ",\"n_spots_total\":" + std::to_string(r.n_spots_total) +
+                                 ",\"num_strong_pixels\":" + std::to_string(r.num_strong_pixels);
+                if (args.output_for_index) js += ",\"spot_centers\":[" + centers + "]";
+                pipe->send(js + "}");
+            }
+            printf("Thread %2d finished image %4u with %5u strong pixels, %4u filtered reflections (%u pixels)\n",
+                   thread_of[image_num], image_num, r.num_strong_pixels, r.n_spots_total, r.num_strong_pixels_filtered);
+            completed++;
+        }
+    };
+
+    {
+        std::vector<std::thread> threads;
+        for (uint32_t t = 0; t < args.threads; ++t) threads.emplace_back(worker, (int)t);
+        std::thread coll(collector);
+        for (auto& t : threads) t.join();
+        coll.join();
+    }
+
+    if (rotation) {  // spotfinder.cc:1099-1150 + find_3d_components (connected_components.cc:448-470)
+        printf("Processing 3D spots\n");
+        ffs_spot* s3 = nullptr;
+        size_t n3 = 0;
+        if (ffs_sweep_finish(ctx, &s3, &n3) != FFS_OK) {
+            printf("Error: 3D connected components failed: %s\n", ffs_last_error(ctx));
+            return 1;
+        }
+        printf("Calculated %zu spots\n", n3);
+        size_t rs = 0, rp = 0;
+        const size_t kept = ffs_filter_spots(s3, n3, args.min_spot_size_3d, args.max_peak_centroid_separation, &rs, &rp);
+        if (rs > 0) printf("Filtered %zu spots with size < %u pixels\n", rs, args.min_spot_size_3d);
+        if (rp > 0) printf("Filtered %zu spots with peak-centroid distance > %s\n", rp, shortest(args.max_peak_centroid_separation).c_str());
+        printf("Found %zu spots\n", kept);
+        if (args.writeout) {
+            std::ofstream out("3d_reflections.txt");
+            for (size_t i = 0; i < kept; ++i)
+                out << "X: [" << s3[i].x_min << ", " << s3[i].x_max << "] Y: [" << s3[i].y_min << ", " << s3[i].y_max
+                    << "] Z: [" << s3[i].z_min << ", " << s3[i].z_max << "] COM: (" << s3[i].com_x << ", " << s3[i].com_y
+                    << ", " << s3[i].com_z << ")\n";
+        }
+        ffs_free(s3);
+    }
+
+    const double total_time = seconds_since(all_images_start);
+    const uint32_t done = completed;
+    printf("\n%u images in %.2f s (%.2f GBps) (%.1f fps)\n", done, total_time,
+           (double)px * sizeof(pixel_t) * done / total_time / 1e9, done / total_time);
+    if (time_waiting_for_images < 10)
+        printf("Total time waiting for images to appear: %.0f ms\n", time_waiting_for_images * 1000);
+    else
+        printf("Total time waiting for images to appear: %.2f s\n", time_waiting_for_images);
+    pipe.reset();
+    ffs_destroy(ctx);
+    return 0;

@@ -1,0 +1,115 @@
+"""The spotfinder / spotfinder32 executables as the Zocalo service drives them
+(src/ffs/service.py:419-507): stream directory in, JSON lines over an inherited pipe fd out,
+stdout line formats (tests/test_spotfinder.py:26-29 of the reference), exit codes."""
+import json
+import os
+import re
+import struct
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from bslz4_ref import compress_chunk
+from ffs_b200 import synth
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+BIN = Path(__file__).resolve().parents[1] / "fast-feedback-service_b200" / "ffs_b200"
+
+
+def write_stream(d: Path, frames, mask, bits, omega_increment=None, start=0):
+    h, w = mask.shape
+    hdr = {"nimages": len(frames), "ntrigger": 1, "y_pixels_in_detector": h, "x_pixels_in_detector": w,
+           "bit_depth_image": bits, "countrate_correction_count_cutoff": 60000, "wavelength": 0.976,
+           "detector_distance": 150.0, "y_pixel_size": 7.5e-5, "x_pixel_size": 7.5e-5,
+           "beam_center_x": w / 2, "beam_center_y": h / 2}
+    if omega_increment is not None:
+        hdr.update(omega_start=0.0, omega_increment=omega_increment)
+    (d / "start_1").write_text(json.dumps(hdr))
+    (d / "start_4").write_bytes(b"")
+    (d / "start_5").write_bytes((mask == 0).astype(np.int32).tobytes())
+    for i, f in enumerate(frames):
+        (d / f"image_{start + i:06d}_2").write_bytes(compress_chunk(f))
+
+
+def run(exe, args, timeout=120):
+    r, w = os.pipe()
+    proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=subprocess.PIPE,
+                            stderr=subprocess.PIPE)
+    os.close(w)
+    lines = []
+    with os.fdopen(r) as f:
+        for line in f:
+            lines.append(json.loads(line))
+    out, err = proc.communicate(timeout=timeout)
+    return proc.returncode, lines, out.decode(), err.decode()
+
+
+def test_stills_json_lines_and_stdout(tmp_path):
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 5, np.uint16, config=8, n_spots=12)
+    write_stream(tmp_path, frames, mask, 16)
+    rc, lines, out, err = run("spotfinder", [str(tmp_path), "--threads", "3", "--output-for-index",
+                                              "--detector", json.dumps({"pixel_size_x": 0.075, "pixel_size_y": 0.075,
+                                                                        "beam_center_x": 11.0, "beam_center_y": 7.5,
+                                                                        "distance": 150.0, "image_size_x": 300,
+                                                                        "detector": "Eiger"})])
+    assert rc == 0 and err == ""
+    assert sorted(l["file-number"] for l in lines) == list(range(5))
+    found = {int(m.group(1)): int(m.group(2)) for m in re.finditer(r"image\s+(\d+).*?(\d+)\s+strong pixels", out)}
+    for l in lines:
+        i = l["file-number"]
+        assert list(l) == ["file", "file-number", "n_spots_total", "num_strong_pixels", "spot_centers"]
+        assert l["file"] == str(tmp_path)
+        strong = oracle.dispersion(frames[i], mask)
+        _, spots = oracle.connected_components(strong, frames[i], want_labels=False)
+        kept, _, _ = oracle.filter_spots(spots, 3, 2.0)
+        assert l["num_strong_pixels"] == int(strong.sum()) == found[i]
+        assert l["n_spots_total"] == int((spots["num_pixels"] >= 3).sum())
+        want = np.stack([kept["com_x"], kept["com_y"], kept["com_z"]], axis=1).astype(np.float64).ravel()
+        np.testing.assert_allclose(np.array(l["spot_centers"]), want, rtol=1e-5)
+    assert re.search(r"\n5 images in [\d.]+ s \([\d.]+ GBps\) \([\d.]+ fps\)", out)
+
+
+def test_bit_depth_exit_code_and_spotfinder32(tmp_path):
+    g = synth.small_geometry(200, 150)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 2, np.uint32, config=5, n_spots=8)
+    write_stream(tmp_path, frames, mask, 32)
+    rc, lines, out, _ = run("spotfinder", [str(tmp_path)])
+    assert rc == 32 and not lines and "Data type mismatch" in out  # service relaunches spotfinder32 on 32
+    rc, lines, out, err = run("spotfinder32", [str(tmp_path), "-a", "dispersion_extended"])
+    assert rc == 0 and err == ""
+    for l in lines:
+        want = oracle.dispersion_extended(frames[l["file-number"]], mask)
+        assert l["num_strong_pixels"] == int(want.sum())
+
+
+def test_rotation_sweep_3d_and_start_index(tmp_path):
+    g = synth.small_geometry(240, 180)
+    mask = synth.make_mask(g)
+    sweep = synth.make_sweep(g, mask, 8, np.uint16, n_reflections=40)
+    write_stream(tmp_path, sweep, mask, 16, omega_increment=0.1)
+    rc, lines, out, err = run("spotfinder", [str(tmp_path), "--threads", "2", "--writeout", "--start-index", "2",
+                                              "--images", "6"])
+    assert rc == 0 and err == ""
+    assert sorted(l["file-number"] for l in lines) == list(range(6))  # 0-based loop counter (N16)
+    strong = np.stack([oracle.dispersion(f, mask) for f in sweep[2:]])
+    _, spots = oracle.connected_components(strong, sweep[2:], want_labels=False)
+    kept, rs, rp = oracle.filter_spots(spots, 3, 2.0)
+    assert int(re.search(r"Calculated\s+(\d+)\s+spots", out).group(1)) == len(spots)
+    if rs:
+        assert int(re.search(r"Filtered\s+(\d+)\s+spots with size < 3 pixels", out).group(1)) == rs
+    if rp:
+        assert int(re.search(r"Filtered\s+(\d+)\s+spots with peak-centroid distance > 2", out).group(1)) == rp
+    assert int(re.search(r"Found (\d+) spots", out).group(1)) == len(kept)
+
+
+def test_list_devices_and_bad_args():
+    out = subprocess.run([str(BIN / "spotfinder"), "--list-devices"], capture_output=True, text=True)
+    assert out.returncode == 0 and re.search(r"0: .+ \(CUDA \d+\.\d+\)", out.stdout)  # service.py:220-238 probes this
+    assert subprocess.run([str(BIN / "spotfinder")], capture_output=True).returncode == 1
+    assert subprocess.run([str(BIN / "spotfinder"), "/tmp", "-a", "sobel"], capture_output=True).returncode == 1
