@@ -14,6 +14,7 @@ extern "C" int ffs_sweep_begin(ffs_ctx* c, uint64_t max_frames) {
     c->sweep_value.reserve(max_frames);
     c->sweep_plane[0].clear();
     c->sweep_plane[1].clear();
+    c->sweep_sums.clear();
     return FFS_OK;
 }
 
@@ -72,10 +73,11 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
              *d_n = nullptr;
     SpotAcc* d_acc = nullptr;
     ffs_spot* d_spots = nullptr;
+    unsigned long long* d_sums = nullptr;
     int rc = FFS_OK;
     auto cleanup = [&]() {
         cudaFree(d_fo); cudaFree(d_idx); cudaFree(d_val); cudaFree(d_z); cudaFree(d_par);
-        cudaFree(d_rank); cudaFree(d_n); cudaFree(d_acc); cudaFree(d_spots);
+        cudaFree(d_rank); cudaFree(d_n); cudaFree(d_acc); cudaFree(d_spots); cudaFree(d_sums);
     };
 #define SWEEP_CK(call)                                                        \
     do {                                                                      \
@@ -95,6 +97,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     SWEEP_CK(cudaMalloc(&d_n, 4));
     SWEEP_CK(cudaMalloc(&d_acc, total * sizeof(SpotAcc)));
     SWEEP_CK(cudaMalloc(&d_spots, total * sizeof(ffs_spot)));
+    SWEEP_CK(cudaMalloc(&d_sums, total * 4 * sizeof(unsigned long long)));
     SWEEP_CK(cudaMemcpy(d_fo, fo.data(), (nz + 1) * 4, cudaMemcpyHostToDevice));
     SWEEP_CK(cudaMemcpy(d_idx, idx.data(), total * 4, cudaMemcpyHostToDevice));
     SWEEP_CK(cudaMemcpy(d_val, val.data(), total * 4, cudaMemcpyHostToDevice));
@@ -105,7 +108,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     a.n_slices = (uint32_t)nz;
     a.total = (uint32_t)total;
     a.fo = d_fo; a.idx = d_idx; a.val = d_val; a.zarr = d_z;
-    a.parent = d_par; a.rank = d_rank; a.acc = d_acc; a.spots = d_spots;
+    a.parent = d_par; a.rank = d_rank; a.acc = d_acc; a.spots = d_spots; a.sums = d_sums;
     a.cap_spots = (uint32_t)total;
     a.n_components = d_n;
     a.row_wrap = c->p.cc_row_wrap;
@@ -125,6 +128,8 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
         return FFS_ERR_NOMEM;
     }
     if (n) SWEEP_CK(cudaMemcpy(out, d_spots, sizeof(ffs_spot) * n, cudaMemcpyDeviceToHost));
+    c->sweep_sums.assign((size_t)n * 4, 0);
+    if (n) SWEEP_CK(cudaMemcpy(c->sweep_sums.data(), d_sums, sizeof(uint64_t) * 4 * n, cudaMemcpyDeviceToHost));
     // boundary planes for slab-sharded sweeps: {linear index, component rank} of the first
     // and last slice
     {
@@ -157,5 +162,16 @@ extern "C" int ffs_sweep_export_plane(ffs_ctx* c, int which, uint32_t** pairs, s
     *pairs = (uint32_t*)malloc(pl.size() * 4);
     if (!*pairs) return FFS_ERR_NOMEM;
     memcpy(*pairs, pl.data(), pl.size() * 4);
+    return FFS_OK;
+}
+
+extern "C" int ffs_sweep_export_sums(ffs_ctx* c, uint64_t** sums, size_t* n_spots) {
+    if (!c || !sums || !n_spots) return FFS_ERR_ARG;
+    *n_spots = c->sweep_sums.size() / 4;
+    *sums = nullptr;
+    if (c->sweep_sums.empty()) return FFS_OK;
+    *sums = (uint64_t*)malloc(c->sweep_sums.size() * sizeof(uint64_t));
+    if (!*sums) return FFS_ERR_NOMEM;
+    memcpy(*sums, c->sweep_sums.data(), c->sweep_sums.size() * sizeof(uint64_t));
     return FFS_OK;
 }

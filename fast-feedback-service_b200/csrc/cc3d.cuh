@@ -19,6 +19,7 @@ struct CC3Args {
     uint32_t* rank;            // [total] output order of a root's spot
     SpotAcc* acc;              // [total]
     ffs_spot* spots;           // [cap_spots]
+    unsigned long long* sums;  // [cap_spots][4] exact sum I, sum (2x+1)I, sum (2y+1)I, sum (2z+1)I
     uint32_t cap_spots;
     uint32_t* n_components;    // device scalar
     int row_wrap;
@@ -90,6 +91,10 @@ __global__ void __launch_bounds__(256) cc3_finalize_kernel(const CC3Args a) {
                 const uint32_t pk = a.idx[pid];
                 acc_to_spot(r, (uint64_t)a.zarr[i] * px + a.idx[i], pk % W, pk / W, (int32_t)a.zarr[pid],
                             a.spots + rank);
+                a.sums[4ull * rank + 0] = r.sum_i;
+                a.sums[4ull * rank + 1] = r.sum_xi;
+                a.sums[4ull * rank + 2] = r.sum_yi;
+                a.sums[4ull * rank + 3] = r.sum_zi;
             }
         }
     }

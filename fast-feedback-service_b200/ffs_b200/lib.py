@@ -102,6 +102,7 @@ SYMBOLS = {
     "ffs_sweep_record_slot": (_i, [_vp, _i, C.c_uint64]),
     "ffs_sweep_finish": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_plane": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_sweep_export_sums": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_free": (None, [_vp]),
     "ffs_filter_spots": (_sz, [_vp, _sz, C.c_uint32, C.c_float, C.POINTER(_sz), C.POINTER(_sz)]),
     "ffs_kernel_launches": (C.c_uint64, [_vp]),

@@ -257,3 +257,14 @@ class Spotfinder:
         ms, n = C.c_double(0), C.c_uint64(0)
         self._ck(self._L.ffs_profile_read(self._ctx, C.byref(ms), C.byref(n)), "ffs_profile_read")
         return ms.value, n.value
+
+    def sweep_export_sums(self) -> np.ndarray:
+        """(n, 4) uint64 exact sums {I, (2x+1)I, (2y+1)I, (2z+1)I} of the last sweep_finish."""
+        ptr, n = C.c_void_p(), C.c_size_t(0)
+        self._ck(self._L.ffs_sweep_export_sums(self._ctx, C.byref(ptr), C.byref(n)), "ffs_sweep_export_sums")
+        if not n.value:
+            return np.zeros((0, 4), np.uint64)
+        buf = (C.c_uint64 * (4 * n.value)).from_address(ptr.value)
+        out = np.frombuffer(buf, dtype=np.uint64).reshape(-1, 4).copy()
+        self._L.ffs_free(ptr)
+        return out

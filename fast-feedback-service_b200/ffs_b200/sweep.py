@@ -1,0 +1,124 @@
+"""Slab-sharded rotation sweeps: merge per-GPU 3D components across slab boundaries.
+
+The reference labels a whole sweep on one host after the last frame
+(ConnectedComponents::find_3d_components, connected_components.cc:270-470).  Here each rank
+owns a contiguous slab of frames and labels it on its GPU (ffs_sweep_finish); components can
+only continue across a slab boundary through pixels with the SAME linear index in the last
+frame of slab r and the first frame of slab r+1 (cc:352-370).  So the exchange is: every rank
+publishes {its unfiltered spots, their exact integer sums, its first / last strong plane as
+(linear index, component) pairs}; boundary planes are intersected, the touching components
+are unioned, and merged spots are recomputed from the exact sums with the reference's own
+arithmetic (double divide -> float centre of mass, float peak-centroid distance).  Canonical
+label / output order = minimum (z, linear index), as on a single GPU.
+
+`merge_slabs` is pure numpy (host logic, unit-tested on CPU); `gather_and_merge` moves the
+KB-sized tables with torch.distributed (NCCL over NVLink on GPUs, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from .lib import SPOT_DTYPE
+
+
+@dataclass
+class SlabResult:
+    z0: int                 # global index of the slab's first frame
+    n_frames: int
+    spots: np.ndarray       # SPOT_DTYPE, z local to the slab, canonical order
+    sums: np.ndarray        # (n, 4) uint64: sum I, (2x+1)I, (2y+1)I, (2z+1)I  (z local)
+    first: np.ndarray       # (k, 2) uint32 {linear index, component} of the slab's first frame
+    last: np.ndarray        # (k, 2) uint32 of its last frame
+
+
+def slab_bounds(n_frames: int, world: int, rank: int) -> tuple[int, int]:
+    """Contiguous slabs: rank r owns frames [r*F/G, (r+1)*F/G)."""
+    return rank * n_frames // world, (rank + 1) * n_frames // world
+
+
+def _find(parent, i):
+    while parent[i] != i:
+        parent[i] = parent[parent[i]]
+        i = parent[i]
+    return i
+
+
+def merge_slabs(slabs: list[SlabResult], width: int, height: int) -> np.ndarray:
+    """All 3D components of the sweep (unfiltered, canonical order) from per-slab results."""
+    slabs = sorted(slabs, key=lambda s: s.z0)
+    px = width * height
+    offs = np.cumsum([0] + [len(s.spots) for s in slabs])
+    n = int(offs[-1])
+    if n == 0:
+        return np.zeros(0, SPOT_DTYPE)
+    spots = np.concatenate([s.spots for s in slabs]).copy()
+    sums = np.concatenate([s.sums.reshape(-1, 4) for s in slabs]).astype(object)  # exact big ints
+    # globalise z (slab-local -> sweep): bbox, peak, label, and sum (2z+1)I += 2*z0*sum I
+    for s, a, b in zip(slabs, offs[:-1], offs[1:]):
+        spots["z_min"][a:b] += s.z0
+        spots["z_max"][a:b] += s.z0
+        spots["peak_z"][a:b] += s.z0
+        spots["label"][a:b] += np.uint64(s.z0 * px)
+        sums[a:b, 3] += 2 * s.z0 * sums[a:b, 0]
+    parent = list(range(n))
+    for k in range(len(slabs) - 1):
+        lo, hi = slabs[k], slabs[k + 1]
+        if lo.z0 + lo.n_frames != hi.z0 or not len(lo.last) or not len(hi.first):
+            continue  # not adjacent frames, or nothing strong on one side
+        _, ia, ib = np.intersect1d(lo.last[:, 0], hi.first[:, 0], assume_unique=True, return_indices=True)
+        for ca, cb in set(zip((lo.last[ia, 1] + offs[k]).tolist(), (hi.first[ib, 1] + offs[k + 1]).tolist())):
+            ra, rb = _find(parent, ca), _find(parent, cb)
+            if ra != rb:  # smaller global id (= smaller (z, index)) stays root
+                parent[max(ra, rb)] = min(ra, rb)
+    roots = np.array([_find(parent, i) for i in range(n)])
+    touched = np.flatnonzero(roots != np.arange(n))
+    for i in touched:  # fold member i into its root r (r < i, so r keeps the canonical label)
+        r = roots[i]
+        a, b = spots[r], spots[i]
+        for f in ("x_min", "y_min", "z_min"):
+            a[f] = min(a[f], b[f])
+        for f in ("x_max", "y_max", "z_max"):
+            a[f] = max(a[f], b[f])
+        a["num_pixels"] += b["num_pixels"]
+        a["sum_intensity"] += b["sum_intensity"]
+        # peak: brightest, ties -> smallest (z, y, x)  (connected_components.cc:143-157)
+        ka = (-int(a["peak_intensity"]), int(a["peak_z"]), int(a["peak_y"]), int(a["peak_x"]))
+        kb = (-int(b["peak_intensity"]), int(b["peak_z"]), int(b["peak_y"]), int(b["peak_x"]))
+        if kb < ka:
+            for f in ("peak_intensity", "peak_x", "peak_y", "peak_z"):
+                a[f] = b[f]
+        sums[r] += sums[i]
+    # Reflection3D::center_of_mass / peak_centroid_distance, recomputed from the exact sums for
+    # every surviving spot: merged ones changed, and slab-local z became sweep z for the rest
+    for r in np.flatnonzero(roots == np.arange(n)):
+        wt = float(sums[r, 0])
+        s = spots[r]
+        if wt == 0:
+            s["com_x"] = s["com_y"] = s["com_z"] = s["peak_centroid_distance"] = np.nan
+            continue
+        com = [np.float32((float(sums[r, k]) * 0.5) / wt) for k in (1, 2, 3)]
+        s["com_x"], s["com_y"], s["com_z"] = com
+        d = [np.float32(np.float32(s[f]) + np.float32(0.5)) - c for f, c in zip(("peak_x", "peak_y", "peak_z"), com)]
+        s["peak_centroid_distance"] = np.sqrt(np.float32(np.float32(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]))
+    keep = roots == np.arange(n)
+    out = spots[keep]
+    return out[np.argsort(out["label"], kind="stable")]
+
+
+def gather_and_merge(local: SlabResult, width: int, height: int, group=None) -> np.ndarray:
+    """Every rank contributes its slab; every rank returns the merged sweep."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return merge_slabs([local], width, height)
+    gathered = [None] * dist.get_world_size(group)
+    dist.all_gather_object(gathered, local, group=group)
+    return merge_slabs(gathered, width, height)
+
+
+def slab_result_from(sf, z0: int, n_frames: int) -> SlabResult:
+    """Finish the sweep recorded in Spotfinder `sf` and package it for merging."""
+    spots = sf.sweep_finish()
+    return SlabResult(z0, n_frames, spots, sf.sweep_export_sums(), sf.sweep_export_plane(0),
+                      sf.sweep_export_plane(1))

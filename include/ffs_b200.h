@@ -194,6 +194,10 @@ int ffs_sweep_finish(ffs_ctx *ctx, ffs_spot **spots, size_t *n_spots);
  * ffs_b200.sweep in the Python host layer). */
 int ffs_sweep_export_plane(ffs_ctx *ctx, int which, uint32_t **index_and_component,
                            size_t *n_pixels);
+/* Exact integer sums of each 3D component of the last ffs_sweep_finish, in the same order:
+ * 4 values per spot: sum I, sum (2x+1) I, sum (2y+1) I, sum (2z+1) I (z local to the slab).
+ * These are what slab merging needs; centroids alone cannot be merged. */
+int ffs_sweep_export_sums(ffs_ctx *ctx, uint64_t **sums, size_t *n_spots);
 void ffs_free(void *p);
 
 /* filter_reflections (connected_components.cc:207-236): stable, in place; returns kept. */

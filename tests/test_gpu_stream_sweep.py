@@ -78,3 +78,29 @@ def test_sweep_3d_components(row_wrap):
         kept, rs, rp = sf.filter_spots(got2, 3, 2.0)
         wk, wrs, wrp = oracle.filter_spots(want, 3, 2.0)
         assert (len(kept), rs, rp) == (len(wk), wrs, wrp)
+
+
+def test_slab_sharded_sweep_merge_on_device():
+    """configs[3] shape: contiguous frame slabs per rank (here: 3 slabs run one after the other
+    on the one GPU), boundary planes exchanged and merged -> identical to one whole-sweep run."""
+    from ffs_b200.sweep import merge_slabs, slab_bounds, slab_result_from
+    g = synth.small_geometry(320, 240)
+    mask = synth.make_mask(g)
+    nz, world = 14, 3
+    sweep = synth.make_sweep(g, mask, nz, np.uint16, n_reflections=80)
+    strong = np.stack([oracle.dispersion(f, mask) for f in sweep])
+    _, want = oracle.connected_components(strong, sweep, want_labels=False)
+    slabs = []
+    for r in range(world):
+        z0, z1 = slab_bounds(nz, world, r)
+        with Spotfinder(g.width, g.height, np.uint16, mask, n_slots=3) as sf:
+            sf.sweep_begin(z1 - z0)
+            for z in range(z0, z1):
+                sf.submit_copy(z, sweep[z])
+                if sf.pending >= 2:
+                    sf.wait()
+            while sf.pending:
+                sf.wait()
+            slabs.append(slab_result_from(sf, z0, z1 - z0))
+    assert sum(len(s.spots) for s in slabs) > len(want)
+    check_spots(merge_slabs(slabs, g.width, g.height), want)
