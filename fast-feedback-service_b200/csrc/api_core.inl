@@ -48,6 +48,12 @@ static int repack_mask(ffs_ctx* c) {
       c->d_mask, (int)c->p.width, (int)c->p.height, reinterpret_cast<uint32_t*>(c->d_valid_bits),
       c->bits_pitch, c->d_valid_count);
     c->launches++;
+    {
+        const long long groups = (long long)((c->p.width + 7) / 8) * c->p.height;
+        group_info_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, c->stream>>>(
+          c->d_valid_bits, c->bits_pitch, (int)c->p.width, (int)c->p.height, c->d_info, c->info_pitch);
+        c->launches++;
+    }
     unsigned long long n = 0;
     FFS_CK(c, cudaMemcpyAsync(&n, c->d_valid_count, sizeof(n), cudaMemcpyDeviceToHost, c->stream));
     FFS_CK(c, cudaStreamSynchronize(c->stream));
@@ -82,6 +88,9 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     const size_t S = p.n_slots;
     FFS_CK(c, cudaMalloc(&c->d_mask, px));
     FFS_CK(c, cudaMalloc(&c->d_valid_bits, c->bits_stride));
+    c->info_pitch = round_up(2 * (size_t)((p.width + 7) / 8), 16);
+    FFS_CK(c, cudaMalloc(&c->d_info, c->info_pitch * p.height));
+    FFS_CK(c, cudaMemset(c->d_info, 0, c->info_pitch * p.height));
     FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 3));
@@ -122,6 +131,15 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
                               (cuuint32_t)kThreshSR, 1};
         rc = make_tensor_map(c, &c->tm_valid, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, c->d_valid_bits,
                              vdims, vstrides, vbox);
+        if (rc) return rc;
+        cuuint32_t box8[3] = {256u, (cuuint32_t)FusedGeo<uint16_t>::SR, 1};
+        rc = make_tensor_map(c, &c->tm_img8, p16 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32,
+                             3, c->d_frames, dims, strides, box8);
+        if (rc) return rc;
+        cuuint64_t idims[2] = {2 * (cuuint64_t)((p.width + 7) / 8), p.height};
+        cuuint64_t istrides[1] = {c->info_pitch};
+        cuuint32_t ibox[2] = {(cuuint32_t)FusedGeo<uint16_t>::INFO_ROW_BYTES, (cuuint32_t)FusedGeo<uint16_t>::SR};
+        rc = make_tensor_map(c, &c->tm_info, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_info, idims, istrides, ibox);
         if (rc) return rc;
         c->have_tm = true;
     }
@@ -164,6 +182,7 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cc_teardown(c);
     cudaFree(c->d_mask);
     cudaFree(c->d_valid_bits);
+    cudaFree(c->d_info);
     cudaFree(c->d_frames);
     cudaFree(c->d_strong);
     cudaFree(c->d_ext1);
@@ -286,6 +305,8 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.threshold = c->p.threshold;
     a.min_count = c->eff_min_count;
     a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
+    a.sig_k = (float)(c->p.nsig_s * (1.0 - 1e-4));
+    a.thr_floor = (int)std::min(std::floor(c->p.threshold), 1073741824.0);
 }
 
 template <typename PixelT, int PPL>
@@ -332,14 +353,73 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
     return FFS_OK;
 }
 
+// The one-kernel path (dispersion_fused.cuh): TMA streaming + in-kernel exact resolution.
+template <typename PixelT>
+static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+    using G = FusedGeo<PixelT>;
+    constexpr int kStages = 3;
+    constexpr int kWarps = sizeof(PixelT) == 2 ? 4 : 2;
+    auto kern = fused_dispersion_kernel<PixelT, kStages, kWarps>;
+    const int smem = kWarps * G::smem_per_warp(kStages) + 128;
+    static bool attr_done[64] = {};
+    if (!attr_done[c->p.device & 63]) {
+        FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_done[c->p.device & 63] = true;
+    }
+    ThreshArgs a{};
+    fill_thresh_args(c, a, first_slot, n);
+    a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
+    a.force_brute = env_int("FFS_FUSED_DEBUG", 0);  // 2: queue but do not resolve (timing experiments only)
+    {   // rows per warp task: R + 6 a multiple of the stage depth, as large as possible while
+        // every SM's resident warps still get ~2 tasks each
+        const int forced = env_int("FFS_TILE_ROWS", 0);
+        const int resident = std::max(1, (int)(200 * 1024 / G::smem_per_warp(kStages)));
+        const long long want = 2LL * c->sm_count * resident;
+        int best = 4 * 8 - 6;
+        for (int groups = 64; groups >= 8; groups -= 2) {
+            best = groups * 4 - 6;
+            const long long tasks = (long long)n * a.n_strips * ((a.height + best - 1) / best);
+            if (tasks >= want) break;
+        }
+        a.tile_rows = forced > 0 ? std::min(forced, 500) : best;
+    }
+    a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
+    const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
+    const unsigned grid = (unsigned)((tasks + kWarps - 1) / kWarps);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c->prof_on) {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (c->prof_used == c->prof_events.size()) {
+            std::pair<cudaEvent_t, cudaEvent_t> ev;
+            cudaEventCreate(&ev.first);
+            cudaEventCreate(&ev.second);
+            c->prof_events.push_back(ev);
+        }
+        e0 = c->prof_events[c->prof_used].first;
+        e1 = c->prof_events[c->prof_used].second;
+        c->prof_used++;
+    }
+    if (e0) cudaEventRecord(e0, st);
+    kern<<<grid, kWarps * 32, smem, st>>>(c->tm_img8, c->tm_info, a);
+    if (e1) cudaEventRecord(e1, st);
+    c->launches++;
+    FFS_CK(c, cudaGetLastError());
+    return FFS_OK;
+}
+
 static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     FFS_CK(c, cudaMemsetAsync(c->d_strong + (size_t)first_slot * c->bits_stride, 0,
                               c->bits_stride * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_strong_count + first_slot, 0, sizeof(unsigned) * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_cand_count + first_slot, 0, sizeof(unsigned) * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
-    if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
-    return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);
+    static const int two_kernel = env_int("FFS_TWO_KERNEL", 0);  // A/B: the round-1 prefilter + resolve pair
+    if (two_kernel || env_int("FFS_FORCE_BRUTE", 0)) {
+        if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
+        return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);
+    }
+    if (c->p.bytes_per_pixel == 2) return launch_fused<uint16_t>(c, first_slot, n, st);
+    return launch_fused<uint32_t>(c, first_slot, n, st);
 }
 
 extern "C" int ffs_threshold(ffs_ctx* c, int first_slot, int n, void* stream) {

@@ -3,6 +3,7 @@
 #include "context.cuh"
 #include "mask.cuh"
 #include "threshold.cuh"
+#include "dispersion_fused.cuh"
 #include "extended.cuh"
 #include "cc.cuh"
 #include "cc3d.cuh"

@@ -48,7 +48,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    // a transaction-count mismatch would otherwise hang the GPU: trap after ~seconds instead
+    unsigned spins = 0;
     while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 24)) __trap();
     }
 }
 
@@ -75,11 +78,20 @@ __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
 
+// prmt.b32 in its default mode: selector nibble bit 3 replicates the sign bit of the selected
+// byte over the destination byte (__byte_perm masks that bit off).
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
 __device__ __forceinline__ uint4 lds128(const void* p) {
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "r"(smem_u32(p)));
+                 : "r"(smem_u32(p))
+                 : "memory");
     return v;
 }
 

@@ -56,6 +56,8 @@ struct ThreshArgs {
     double nsig_b, nsig_s, threshold;
     int min_count;
     float prefilter_k;  // nsig_s^2 * (1 - 1e-4): conservative
+    float sig_k;        // nsig_s * (1 - 1e-4)            (fused kernel)
+    int thr_floor;      // floor(threshold): v > threshold <=> v > thr_floor for integer v
 };
 
 template <typename PixelT, int KH_, int PPL_, int SR_>
