@@ -318,7 +318,7 @@ def run_gpu_arm(args):
                     "d2h_bytes_per_step": B * (32 + 4096 * 80),
                     "h2d_gbs_per_gpu": n_e2e * frame_bytes / t_e2e / 1e9},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "prefilter_kernel<u16>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "fused_dispersion_kernel<u16> (whole threshold: stream + exact resolve)", "achieved": achieved, "peak": peak,
                          "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic * B if traffic else None, "kernel_ms": k_avg,
                          "algorithmic_bytes_per_launch": alg,

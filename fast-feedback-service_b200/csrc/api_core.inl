@@ -354,11 +354,9 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
 }
 
 // The one-kernel path (dispersion_fused.cuh): TMA streaming + in-kernel exact resolution.
-template <typename PixelT>
-static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+template <typename PixelT, int kWarps, int kStages>
+static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     using G = FusedGeo<PixelT>;
-    constexpr int kStages = 3;
-    constexpr int kWarps = sizeof(PixelT) == 2 ? 4 : 2;
     auto kern = fused_dispersion_kernel<PixelT, kStages, kWarps>;
     const int smem = kWarps * G::smem_per_warp(kStages) + 128;
     static bool attr_done[64] = {};
@@ -369,7 +367,8 @@ static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     ThreshArgs a{};
     fill_thresh_args(c, a, first_slot, n);
     a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
-    a.force_brute = env_int("FFS_FUSED_DEBUG", 0);  // 2: queue but do not resolve (timing experiments only)
+    static const int dbg = env_int("FFS_FUSED_DEBUG", 0);
+    a.force_brute = dbg;  // 2: queue but do not resolve (timing experiments only)
     {   // rows per warp task: R + 6 a multiple of the stage depth, as large as possible while
         // every SM's resident warps still get ~2 tasks each
         const int forced = env_int("FFS_TILE_ROWS", 0);
@@ -405,6 +404,26 @@ static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     c->launches++;
     FFS_CK(c, cudaGetLastError());
     return FFS_OK;
+}
+
+template <typename PixelT>
+static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+    static const int w = env_int("FFS_FUSED_WARPS", 3);  // warps (independent tasks) per CTA
+    static const int stg = env_int("FFS_FUSED_STAGES", 2);
+    if (stg == 2) {
+        switch (w) {
+            case 1: return launch_fused_w<PixelT, 1, 2>(c, first_slot, n, st);
+            case 2: return launch_fused_w<PixelT, 2, 2>(c, first_slot, n, st);
+            case 4: return launch_fused_w<PixelT, 4, 2>(c, first_slot, n, st);
+            default: return launch_fused_w<PixelT, 3, 2>(c, first_slot, n, st);
+        }
+    }
+    switch (w) {
+        case 1: return launch_fused_w<PixelT, 1, 3>(c, first_slot, n, st);
+        case 2: return launch_fused_w<PixelT, 2, 3>(c, first_slot, n, st);
+        case 4: return launch_fused_w<PixelT, 4, 3>(c, first_slot, n, st);
+        default: return launch_fused_w<PixelT, 3, 3>(c, first_slot, n, st);
+    }
 }
 
 static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {

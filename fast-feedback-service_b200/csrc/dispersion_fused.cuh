@@ -34,6 +34,10 @@
 
 namespace ffsb {
 
+#ifndef FUSED_MIN_WARPS_PER_SM
+#define FUSED_MIN_WARPS_PER_SM 12  // register cap = 65536 / (32 * this)
+#endif
+
 template <typename PixelT>
 struct FusedGeo {
     static constexpr int KH = 3;
@@ -54,7 +58,8 @@ struct FusedGeo {
     static constexpr int RING_BYTES = RING_ROWS * RING_ROW_BYTES;
     static constexpr int GQ_CAP = 64;        // pending candidate groups (< 32 + 30)
     static constexpr int PQ_CAP = 288;       // pending candidate pixels (< 32 + 32 * 8)
-    static constexpr int QUEUE_BYTES = (GQ_CAP + PQ_CAP) * 4;
+    // per queued group: 4 B meta + 32 B window sums + 16 B clamped centre-row words
+    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + PQ_CAP * 4;
     static_assert(RING_ROWS > 2 * KH, "ring must hold the 7-row window");
     static_assert(IMG_STAGE_BYTES % 128 == 0 && QUEUE_BYTES % 128 == 0, "TMA destination alignment");
     __host__ __device__ static constexpr int smem_per_warp(int stages) {
@@ -134,17 +139,115 @@ __device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_
     }
 }
 
+// ---- rare path, deliberately NOT inlined (one copy of ~2000 instructions instead of five) ----
+// Expands the last `n` queued groups to candidate pixels with each pixel's own window sum,
+// then resolves the queued pixels 32 at a time (all of them if flush_all) with the exact
+// test.  state = qn | pqn << 8 (both warp-uniform); the new state is returned.
+template <typename PixelT>
+__device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap, uint8_t* qbase,
+                                               const float* rcp_tab, int x0, int r0, int z, uint32_t state,
+                                               int n, bool flush_all) {
+    using G = FusedGeo<PixelT>;
+    constexpr int PPL = G::PPL, KH = G::KH;
+    const ThreshArgs& a = *ap;
+    const int lane = threadIdx.x & 31;
+    uint32_t* gq = reinterpret_cast<uint32_t*>(qbase);
+    uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);
+    uint4* cq = hq + 2 * G::GQ_CAP;
+    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);
+    const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
+    const uint8_t* valid = a.valid_bits;
+    const float sk = a.sig_k;
+    const int thr_floor = a.thr_floor;
+    int qn = state & 0xff, pqn = state >> 8;
+    unsigned found = 0;
+    auto resolve_entry = [&](uint32_t e) {
+        const int col = e & 0x1fff, row = e >> 13;
+        if (a.force_brute == 2) return;
+        if (resolve_pixel_wide<PixelT, KH>(a, frame, valid, col, row)) {
+            set_strong(a, z, col, row);
+            ++found;
+        }
+    };
+    if (n > 0) {
+        uint32_t bits = 0;
+        int col0 = 0, row = 0;
+        if (lane < n) {
+            const int qi = qn - n + lane;
+            const uint32_t e = gq[qi];
+            const uint4 ha = hq[2 * qi], hb = hq[2 * qi + 1];
+            const uint32_t hx[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+            const float rc = rcp_tab[e >> 14];
+            col0 = x0 + (int)(e & 31u) * PPL;
+            row = r0 + (int)((e >> 5) & 0x1ffu);
+            uint32_t v[8], vb = 0xffu;
+            if constexpr (sizeof(PixelT) == 2) {
+                // masked + clamped centre-row values queued by the streaming loop: a masked pixel
+                // reads 0 and never passes; a clamped one (== CLAMP) always passes (see below)
+                const uint4 cw = cq[qi];
+                v[0] = cw.x & 0xffffu; v[1] = cw.x >> 16; v[2] = cw.y & 0xffffu; v[3] = cw.y >> 16;
+                v[4] = cw.z & 0xffffu; v[5] = cw.z >> 16; v[6] = cw.w & 0xffffu; v[7] = cw.w >> 16;
+            } else {
+                // 32-bit pixels >= 2^24 are not in the clamped words (they count 0): read the frame
+                vb = valid[(size_t)row * a.valid_pitch + (col0 >> 3)];
+                const PixelT* p = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch) + col0;
+                const uint4 ra = reinterpret_cast<const uint4*>(p)[0], rb = reinterpret_cast<const uint4*>(p)[1];
+                v[0] = ra.x; v[1] = ra.y; v[2] = ra.z; v[3] = ra.w;
+                v[4] = rb.x; v[5] = rb.y; v[6] = rb.z; v[7] = rb.w;
+            }
+            // per-pixel bound: the pixel's own window sum (still a lower bound of x) over m_ub
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float mu = (float)hx[j] * rc;
+                float sq;
+                asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
+                uint32_t T = (uint32_t)max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
+                if constexpr (sizeof(PixelT) == 2) T = min(T, G::CLAMP - 1u);
+                bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
+            }
+        }
+        qn -= n;
+        int cnt = __popc(bits), incl = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        int pos = pqn + incl - cnt;
+        while (bits) {
+            const int j = __ffs(bits) - 1;
+            bits &= bits - 1;
+            pq[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
+        }
+        pqn += __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+        while (pqn >= 32) {
+            pqn -= 32;
+            resolve_entry(pq[pqn + lane]);
+        }
+        __syncwarp();
+    }
+    if (flush_all && pqn > 0) {
+        if (lane < pqn) resolve_entry(pq[lane]);
+        pqn = 0;
+    }
+    for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
+    if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
+    return (uint32_t)qn | ((uint32_t)pqn << 8);
+}
+
 template <typename PixelT, int STAGES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
   fused_dispersion_kernel(const __grid_constant__ CUtensorMap tm_img,
-                          const __grid_constant__ CUtensorMap tm_info, const ThreshArgs a) {
+                          const __grid_constant__ CUtensorMap tm_info,
+                          const __grid_constant__ ThreshArgs a) {
     using G = FusedGeo<PixelT>;
     constexpr int SR = G::SR, KH = G::KH, PPL = G::PPL;
     static_assert(SR == 4, "row loop is written for 4-row stages and an 8-row ring");
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ float rcp_tab[64];  // 0.99999 / m_ub
-    if (threadIdx.x < 64) rcp_tab[threadIdx.x] = 0.99999f / (float)max((int)threadIdx.x, 1);
+    for (int t = threadIdx.x; t < 64; t += WARPS * 32) rcp_tab[t] = 0.99999f / (float)max(t, 1);
     __syncthreads();  // the only block-wide barrier
 
     const int warp = threadIdx.x >> 5;
@@ -161,7 +264,8 @@ __global__ void __launch_bounds__(WARPS * 32)
     uint8_t* stage_base = wsm;
     uint8_t* ring = wsm + STAGES * G::STAGE_BYTES;
     uint32_t* gq = reinterpret_cast<uint32_t*>(ring + G::RING_BYTES);
-    uint32_t* pq = gq + G::GQ_CAP;
+    uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);   // 2 x uint4 per queued group: its 8 window sums
+    uint4* cq = hq + 2 * G::GQ_CAP;                         // its clamped centre-row words
     uint64_t* bars = reinterpret_cast<uint64_t*>(ring + G::RING_BYTES + G::QUEUE_BYTES);
 
     const int r0 = rt * a.tile_rows;
@@ -193,67 +297,12 @@ __global__ void __launch_bounds__(WARPS * 32)
         for (int g = 0; g < STAGES && g < n_groups; ++g) issue(g, g);
     }
 
-    const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
-    const uint8_t* valid = a.valid_bits;
     const bool out_lane = lane >= 1 && lane <= G::OUT_LANES;
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const float sk = a.sig_k;             // nsig_s * (1 - 1e-4)
+    const int thr_floor = a.thr_floor;
     int qn = 0, pqn = 0;     // warp-uniform queue fill levels
-    unsigned found = 0;
-
-    // exact test of one queued pixel
-    auto resolve_entry = [&](uint32_t e) {
-        const int col = e & 0x1fff, row = e >> 13;
-        if (a.force_brute == 2) return;
-        if (resolve_pixel<PixelT, KH, false>(a, frame, valid, col, row)) {
-            set_strong(a, z, col, row);
-            ++found;
-        }
-    };
-    // expand `n` queued groups (the last n of gq) to candidate pixels, then resolve full rounds
-    auto resolve_groups = [&](int n) {
-        uint32_t bits = 0, e = 0;
-        int col0 = 0, row = 0;
-        if (lane < n) {
-            e = gq[qn - n + lane];
-            const uint32_t T = e >> 14;
-            col0 = x0 + (int)(e & 31u) * PPL;
-            row = r0 + (int)((e >> 5) & 0x1ffu);
-            const uint32_t vb = valid[(size_t)row * a.valid_pitch + (col0 >> 3)];
-            const PixelT* p = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch) + col0;
-            uint32_t v[8];
-            if constexpr (sizeof(PixelT) == 2) {
-                const uint4 raw = *reinterpret_cast<const uint4*>(p);
-                v[0] = raw.x & 0xffffu; v[1] = raw.x >> 16; v[2] = raw.y & 0xffffu; v[3] = raw.y >> 16;
-                v[4] = raw.z & 0xffffu; v[5] = raw.z >> 16; v[6] = raw.w & 0xffffu; v[7] = raw.w >> 16;
-            } else {
-                const uint4 ra = reinterpret_cast<const uint4*>(p)[0], rb = reinterpret_cast<const uint4*>(p)[1];
-                v[0] = ra.x; v[1] = ra.y; v[2] = ra.z; v[3] = ra.w;
-                v[4] = rb.x; v[5] = rb.y; v[6] = rb.z; v[7] = rb.w;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
-        }
-        qn -= n;
-        int cnt = __popc(bits), incl = cnt;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, off);
-            if (lane >= off) incl += t;
-        }
-        int pos = pqn + incl - cnt;
-        while (bits) {
-            const int j = __ffs(bits) - 1;
-            bits &= bits - 1;
-            pq[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
-        }
-        pqn += __shfl_sync(0xffffffffu, incl, 31);
-        __syncwarp();
-        while (pqn >= 32) {
-            pqn -= 32;
-            resolve_entry(pq[pqn + lane]);
-        }
-        __syncwarp();
-    };
+    uint8_t* qbase = reinterpret_cast<uint8_t*>(gq);
 
     uint32_t V[4] = {0, 0, 0, 0};   // packed column sums of the last 7 rows
     uint32_t hv1 = 0, hv2 = 0, hv3 = 0;  // max masked value of rows i-1, i-2, i-3
@@ -261,8 +310,6 @@ __global__ void __launch_bounds__(WARPS * 32)
     uint8_t* ring_lane = ring + lane * 16;
     const int pimg_off = lane * PPL * (int)sizeof(PixelT);
     const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 2 * lane;
-    const float sk = a.sig_k;             // nsig_s * (1 - 1e-4)
-    const int thr_floor = a.thr_floor;
 
     int s = 0;
     uint32_t phase = 0;
@@ -271,13 +318,17 @@ __global__ void __launch_bounds__(WARPS * 32)
         const uint8_t* st = stage_base + s * G::STAGE_BYTES;
         uint8_t* rcur = ring_lane + ((g & 1) ? SR * G::RING_ROW_BYTES : 0);
         uint8_t* roth = ring_lane + ((g & 1) ? 0 : SR * G::RING_ROW_BYTES);
+        if (a.force_brute != 5) {  // 5: timing experiment, TMA traffic only
+        // The stage body is written in three straight-line phases so that the four rows'
+        // dependent chains (LDS -> sums -> SHFL -> sums -> MUFU -> VOTE) interleave.
+        // ---- phase A: load, mask, clamp, vertical running sums, ring update ------------------
+        uint32_t Vs[SR][4], vmc[SR], mub[SR];
 #pragma unroll
         for (int u = 0; u < SR; ++u) {
-            const int i = g * SR + u;  // load-row index within the task
             uint32_t c[4], vm, info;
             fused_load_row<PixelT>(st + u * G::IMG_ROW_BYTES + pimg_off, st + pinfo_off + u * G::INFO_ROW_BYTES,
                                    c, vm, info);
-            // vertical running sum over 7 rows: V += row(i) - row(i-7); ring slot of row i = i & 7
+            // V += row(i) - row(i-7); ring slot of row i = i & 7
             uint8_t* oldp = (u + 1 < SR) ? rcur + (u + 1) * G::RING_ROW_BYTES : roth;
             const uint4 old = ptx::lds128(oldp);
             V[0] = V[0] + c[0] - old.x;
@@ -285,52 +336,73 @@ __global__ void __launch_bounds__(WARPS * 32)
             V[2] = V[2] + c[2] - old.z;
             V[3] = V[3] + c[3] - old.w;
             *reinterpret_cast<uint4*>(rcur + u * G::RING_ROW_BYTES) = make_uint4(c[0], c[1], c[2], c[3]);
-
-            const int out_row = r0 + i - 2 * KH;
-            if (i >= 2 * KH && out_row < row_end) {  // warp-uniform
-                // horizontal 7-tap sums of the column sums, 32-bit
-                const uint32_t l2 = __shfl_up_sync(0xffffffffu, V[2], 1);
-                const uint32_t l3 = __shfl_up_sync(0xffffffffu, V[3], 1);
-                const uint32_t rr0 = __shfl_down_sync(0xffffffffu, V[0], 1);
-                const uint32_t rr1 = __shfl_down_sync(0xffffffffu, V[1], 1);
-                uint32_t E[14];
-                E[0] = l2 >> 16;
-                E[1] = l3 & 0xffffu;
-                E[2] = l3 >> 16;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    E[3 + 2 * k] = V[k] & 0xffffu;
-                    E[4 + 2 * k] = V[k] >> 16;
-                }
-                E[11] = rr0 & 0xffffu;
-                E[12] = rr0 >> 16;
-                E[13] = rr1 & 0xffffu;
-                uint32_t h = E[0] + E[1] + E[2] + E[3] + E[4] + E[5] + E[6];
-                uint32_t xmin = h;
-#pragma unroll
-                for (int j = 1; j < 8; ++j) {
-                    h = h + E[j + 6] - E[j - 1];
-                    xmin = min(xmin, h);
-                }
-                // group threshold on the raw value: T = floor(mu + nsig_s' sqrt(mu)), mu = x_lb / m_ub
-                const float mu = (float)xmin * rcp_tab[hi3 >> 8];
-                float sq;
-                asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
-                int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
-                if (a.force_brute == 3) T = thr_floor;  // debug: no pruning
-                const bool pass = out_lane && hv3 > (uint32_t)T;
-                const unsigned ball = __ballot_sync(0xffffffffu, pass);
-                if (ball) {
-                    if (pass)
-                        gq[qn + __popc(ball & lt_mask)] =
-                          (uint32_t)lane | ((uint32_t)(out_row - r0) << 5) | ((uint32_t)min(T, 0x3ffff) << 14);
-                    qn += __popc(ball);
-                    __syncwarp();
-                    if (qn >= 32) resolve_groups(32);
-                }
-            }
+            for (int k = 0; k < 4; ++k) Vs[u][k] = V[k];
+            vmc[u] = hv3;          // centre row (i - 3): max masked value and m_ub
+            mub[u] = hi3 >> 8;
             hv3 = hv2; hv2 = hv1; hv1 = vm;
             hi3 = hi2; hi2 = hi1; hi1 = info;
+        }
+        // ---- phase B: horizontal sums, group threshold, pass flag (no branches) --------------
+        uint32_t Hx[SR][8];
+        bool pass[SR];
+#pragma unroll
+        for (int u = 0; u < SR; ++u) {
+            const int i = g * SR + u;  // load-row index within the task
+            const int out_row = r0 + i - 2 * KH;
+            const uint32_t l2 = __shfl_up_sync(0xffffffffu, Vs[u][2], 1);
+            const uint32_t l3 = __shfl_up_sync(0xffffffffu, Vs[u][3], 1);
+            const uint32_t rr0 = __shfl_down_sync(0xffffffffu, Vs[u][0], 1);
+            const uint32_t rr1 = __shfl_down_sync(0xffffffffu, Vs[u][1], 1);
+            uint32_t E[14];
+            E[0] = l2 >> 16;
+            E[1] = l3 & 0xffffu;
+            E[2] = l3 >> 16;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                E[3 + 2 * k] = Vs[u][k] & 0xffffu;
+                E[4 + 2 * k] = Vs[u][k] >> 16;
+            }
+            E[11] = rr0 & 0xffffu;
+            E[12] = rr0 >> 16;
+            E[13] = rr1 & 0xffffu;
+            Hx[u][0] = E[0] + E[1] + E[2] + E[3] + E[4] + E[5] + E[6];
+            uint32_t xmin = Hx[u][0];
+#pragma unroll
+            for (int j = 1; j < 8; ++j) {
+                Hx[u][j] = Hx[u][j - 1] + E[j + 6] - E[j - 1];
+                xmin = min(xmin, Hx[u][j]);
+            }
+            // group threshold on the raw value: T = floor(mu + nsig_s' sqrt(mu)), mu = x_lb / m_ub
+            const float mu = (float)xmin * rcp_tab[mub[u]];
+            float sq;
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
+            const int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
+            pass[u] = out_lane && vmc[u] > (uint32_t)T && i >= 2 * KH && out_row < row_end;
+        }
+        // ---- phase C: queue the passing groups; resolve when 32 are pending -------------------
+#pragma unroll
+        for (int u = 0; u < SR; ++u) {
+            const unsigned ball = __ballot_sync(0xffffffffu, pass[u]);
+            if (ball) {
+                if (pass[u]) {
+                    const int qi = qn + __popc(ball & lt_mask);
+                    gq[qi] = (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[u] << 14);
+                    hq[2 * qi] = make_uint4(Hx[u][0], Hx[u][1], Hx[u][2], Hx[u][3]);
+                    hq[2 * qi + 1] = make_uint4(Hx[u][4], Hx[u][5], Hx[u][6], Hx[u][7]);
+                    // ring slot of the centre row i-3 is (i + 5) & 7
+                    cq[qi] = ptx::lds128((u < SR - 1) ? roth + (u + 1) * G::RING_ROW_BYTES : rcur);
+                }
+                qn += __popc(ball);
+                __syncwarp();
+                if (qn >= 32) {
+                    const uint32_t st2 = fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z,
+                                                               (uint32_t)qn | ((uint32_t)pqn << 8), 32, false);
+                    qn = st2 & 0xff;
+                    pqn = st2 >> 8;
+                }
+            }
+        }
         }
         // refill the stage we just consumed
         __syncwarp();
@@ -344,10 +416,8 @@ __global__ void __launch_bounds__(WARPS * 32)
         }
     }
     __syncwarp();
-    if (qn > 0) resolve_groups(qn);
-    if (lane < pqn) resolve_entry(pq[lane]);
-    for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
-    if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
+    if (qn > 0 || pqn > 0)
+        fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
 }
 
 }  // namespace ffsb

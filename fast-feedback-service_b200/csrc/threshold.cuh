@@ -146,6 +146,80 @@ __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t
     return aa > cc;
 }
 
+// Same decision as resolve_pixel (standard dispersion), gathering each window row with 16-byte
+// loads: a scattered gather is bound by L1 wavefronts (one per distinct line touched per
+// lane), so 2-3 wide loads + 2 validity bytes per row replace 7 + 3 narrow ones.
+template <typename PixelT, int KH>
+__device__ __forceinline__ bool resolve_pixel_wide(const ThreshArgs& a, const uint8_t* frame,
+                                                   const uint8_t* valid, int col, int row) {
+    constexpr int PC = 16 / (int)sizeof(PixelT);           // pixels per 16-byte chunk
+    constexpr int NCH = sizeof(PixelT) == 2 ? 2 : 3;       // chunks covering any 7-pixel window
+    // the caller has already established mask[k] for the centre pixel
+    const int y0 = max(row - KH, 0), y1 = min(row + KH, a.height - 1);
+    const int xs = col - KH;                               // may be negative
+    const int ch0 = xs >> (sizeof(PixelT) == 2 ? 3 : 2);   // floor(xs / PC)
+    const int base_px = ch0 * PC;
+    const int n_chunks = (int)(a.pitch >> 4);
+    const int vb0 = base_px >> 3;                          // floor; base_px is a multiple of 4
+    const uint32_t win = 0x7fu << (xs - base_px);
+    uint32_t m = 0, x = 0;
+    unsigned long long y = 0;
+    // all rows unrolled so that the loads of the whole window are in flight together
+#pragma unroll
+    for (int dy = -KH; dy <= KH; ++dy) {
+        const int yy = row + dy;
+        const bool in_rows = yy >= y0 && yy <= y1;
+        const int yc = min(max(yy, y0), y1);
+        const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)yc * a.pitch);
+        const uint8_t* vrow = valid + (size_t)yc * a.valid_pitch;
+        uint32_t bits = 0;
+        if (in_rows && vb0 >= 0 && vb0 < (int)a.valid_pitch) bits = vrow[vb0];
+        if (in_rows && vb0 + 1 >= 0 && vb0 + 1 < (int)a.valid_pitch) bits |= (uint32_t)vrow[vb0 + 1] << 8;
+        if (sizeof(PixelT) == 4) bits >>= (base_px & 4);
+        const uint32_t sel = bits & win;
+        uint4 ch[NCH];
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+            const int ci = ch0 + k;
+            ch[k] = (ci >= 0 && ci < n_chunks) ? prow[ci] : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+            const uint32_t wv[4] = {ch[k].x, ch[k].y, ch[k].z, ch[k].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if constexpr (sizeof(PixelT) == 2) {
+                    const uint32_t lo = (sel >> (k * 8 + 2 * q)) & 1u ? (wv[q] & 0xffffu) : 0u;
+                    const uint32_t hi = (sel >> (k * 8 + 2 * q + 1)) & 1u ? (wv[q] >> 16) : 0u;
+                    x += lo + hi;
+                    y += (unsigned long long)lo * lo;
+                    y += (unsigned long long)hi * hi;
+                } else {
+                    // int mm = (mask[k] && src[k] < BIG) ? 1 : 0;   standalone.cc:90
+                    const bool counted = ((sel >> (k * 4 + q)) & 1u) && wv[q] < (1u << 24);
+                    const uint32_t pv = counted ? wv[q] : 0u;
+                    m += counted ? 1u : 0u;
+                    x += pv;
+                    y += (unsigned long long)pv * pv;
+                }
+            }
+        }
+        if constexpr (sizeof(PixelT) == 2) m += __popc(sel);
+    }
+    const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    const double md = (double)m, xd = (double)x, yd = (double)y;
+    if (!((int)m >= a.min_count)) return false;
+    if (!(vd > a.threshold)) return false;
+    const double b = __dsub_rn(__dmul_rn(md, vd), xd);
+    const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
+    if (!(b > d)) return false;
+    const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
+                                __dmul_rn(xd, __dsub_rn(md, 1.0)));
+    const double cc =
+      __dmul_rn(__dmul_rn(xd, a.nsig_b), __dsqrt_rn(__dmul_rn(2.0, __dsub_rn(md, 1.0))));
+    return aa > cc;
+}
+
 __device__ __forceinline__ void set_strong(const ThreshArgs& a, int z, int col, int row) {
     uint32_t* w = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(a.strong_bits) +
                                               (size_t)z * a.strong_frame_stride +

@@ -16,7 +16,7 @@ sf = Spotfinder(geom.width, geom.height, dtype, mask, n_slots=nslots, algorithm=
 sf.upload(frames)
 st = torch.cuda.Stream()
 fn = sf.process if os.environ.get("PROCESS") else sf.threshold
-for batch in [1, 2, 4, 8, 16, 32]:
+for batch in [int(b) for b in os.environ.get("BATCHES", "1,2,4,8,16,32").split(",")]:
     if batch > nslots: break
     for _ in range(3):
         fn(0, batch, st.cuda_stream, sync=True)
