@@ -1,0 +1,179 @@
+// api_bslz4.inl -- compressed ingestion: upload the raw bitshuffle-LZ4 chunk, decode on the
+// device (bslz4_gpu.cuh), continue with the ordinary per-frame pipeline.
+
+static inline uint32_t be32h(const uint8_t* p) {
+    return (uint32_t)p[0] << 24 | (uint32_t)p[1] << 16 | (uint32_t)p[2] << 8 | p[3];
+}
+
+static int bslz4_setup(ffs_ctx* c) {
+    if (c->h_chunks) return FFS_OK;
+    const size_t S = c->p.n_slots;
+    const size_t es = c->p.bytes_per_pixel;
+    const size_t n = (size_t)c->p.width * c->p.height;
+    const size_t min_block = 128;  // elements; the smallest block bitshuffle ever chooses
+    c->max_blocks = (uint32_t)(n / min_block + 2);
+    // worst case: incompressible data in the smallest blocks -- per block a 4-byte header and
+    // the LZ4 bound (len + len/255 + 16) -- plus the filter header and slack
+    const size_t frame_bytes = n * es;
+    c->chunk_cap = round_up(frame_bytes + frame_bytes / 255 + 20 * (size_t)c->max_blocks + 12 + 64, 256);
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_cap * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_cap * S + 64));
+    FFS_CK(c, cudaHostAlloc(&c->h_blocks, sizeof(uint2) * c->max_blocks * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaMalloc(&c->d_blocks, sizeof(uint2) * c->max_blocks * S));
+    FFS_CK(c, cudaMalloc(&c->d_dec_status, sizeof(unsigned) * S));
+    FFS_CK(c, cudaHostAlloc(&c->h_dec_status, sizeof(unsigned) * S, cudaHostAllocDefault));
+    memset(c->h_dec_status, 0, sizeof(unsigned) * S);
+    return FFS_OK;
+}
+
+static void bslz4_teardown(ffs_ctx* c) {
+    cudaFreeHost(c->h_chunks);
+    cudaFree(c->d_chunks);
+    cudaFreeHost(c->h_blocks);
+    cudaFree(c->d_blocks);
+    cudaFree(c->d_dec_status);
+    cudaFreeHost(c->h_dec_status);
+}
+
+// Walk the block headers of `chunk` (host memory) and fill the slot's block table.
+static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, Bslz4Args& a) {
+    const size_t es = c->p.bytes_per_pixel;
+    const size_t n = (size_t)c->p.width * c->p.height;
+    if (len < 12 || len > c->chunk_cap) return FFS_ERR_FORMAT;
+    const uint64_t total = (uint64_t)be32h(chunk) << 32 | be32h(chunk + 4);
+    if (total != (uint64_t)n * es) return FFS_ERR_FORMAT;
+    size_t block = be32h(chunk + 8) / es;
+    if (block == 0) block = std::max<size_t>((8192 / es) / 8 * 8, 128);  // bshuf_default_block_size
+    if (block % 8 || block * es > (size_t)kBslz4MaxBlockBytes) return FFS_ERR_FORMAT;
+    const size_t full = n / block;
+    size_t last = n % block;
+    last -= last % 8;
+    const size_t n_blocks = full + (last ? 1 : 0);
+    if (n_blocks > c->max_blocks) return FFS_ERR_FORMAT;
+    uint2* tab = c->h_blocks + (size_t)slot * c->max_blocks;
+    size_t pos = 12;
+    for (size_t b = 0; b < n_blocks; ++b) {
+        if (len - pos < 4) return FFS_ERR_FORMAT;
+        const uint32_t clen = be32h(chunk + pos);
+        pos += 4;
+        if (clen > len - pos || clen > (uint32_t)(kBslz4InBytes - 32)) return FFS_ERR_FORMAT;
+        tab[b] = make_uint2((uint32_t)pos, clen);
+        pos += clen;
+    }
+    const size_t tail = n % 8;
+    if (len - pos < tail * es) return FFS_ERR_FORMAT;
+    a.n_blocks = (uint32_t)n_blocks;
+    a.block_elems = (uint32_t)block;
+    a.last_elems = (uint32_t)(last ? last : block);
+    a.tail_off = (uint32_t)pos;
+    a.tail_elems = (uint32_t)tail;
+    a.tail_elem0 = (uint64_t)(n - tail);
+    return FFS_OK;
+}
+
+static int bslz4_launch(ffs_ctx* c, int slot, Bslz4Args& a, cudaStream_t st) {
+    constexpr int kWarps = 4;
+    a.chunk = c->d_chunks + (size_t)slot * c->chunk_cap;
+    a.blocks = c->d_blocks + (size_t)slot * c->max_blocks;
+    a.frame = c->d_frames + (size_t)slot * c->frame_stride;
+    a.pitch = c->pitch;
+    a.width = c->p.width;
+    a.elem_size = c->p.bytes_per_pixel;
+    a.status = c->d_dec_status + slot;
+    const int smem = kWarps * kBslz4SmemPerWarp;
+    const unsigned grid = std::max(1u, (a.n_blocks + kWarps - 1) / kWarps);
+    static bool attr_done[64][2] = {};
+    const int pi = c->p.bytes_per_pixel == 2 ? 0 : 1;
+    if (!attr_done[c->p.device & 63][pi]) {
+        if (pi == 0)
+            FFS_CK(c, cudaFuncSetAttribute(bslz4_decode_kernel<uint16_t, kWarps>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        else
+            FFS_CK(c, cudaFuncSetAttribute(bslz4_decode_kernel<uint32_t, kWarps>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_done[c->p.device & 63][pi] = true;
+    }
+    FFS_CK(c, cudaMemsetAsync(c->d_dec_status + slot, 0, sizeof(unsigned), st));
+    if (pi == 0)
+        bslz4_decode_kernel<uint16_t, kWarps><<<grid, kWarps * 32, smem, st>>>(a);
+    else
+        bslz4_decode_kernel<uint32_t, kWarps><<<grid, kWarps * 32, smem, st>>>(a);
+    c->launches++;
+    FFS_CK(c, cudaGetLastError());
+    return FFS_OK;
+}
+
+extern "C" int ffs_acquire_compressed(ffs_ctx* c, int* slot, void** pinned_chunk, size_t* capacity) {
+    if (!c || !slot || !pinned_chunk) return FFS_ERR_ARG;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        int rc = bslz4_setup(c);
+        if (rc) return rc;
+    }
+    void* frame = nullptr;
+    int rc = ffs_acquire(c, slot, &frame);
+    if (rc) return rc;
+    *pinned_chunk = c->h_chunks + (size_t)*slot * c->chunk_cap;
+    if (capacity) *capacity = c->chunk_cap;
+    return FFS_OK;
+}
+
+extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, size_t chunk_bytes) {
+    if (!slots_ok(c, slot, 1) || !c->h_chunks) return FFS_ERR_ARG;
+    std::unique_lock<std::mutex> lk(c->mu);
+    StreamSlot& s = c->slots[slot];
+    if (s.state != 1) return FFS_ERR_STATE;
+    const uint8_t* chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
+    Bslz4Args a{};
+    int rc = bslz4_index(c, slot, chunk, chunk_bytes, a);
+    if (rc) {
+        c->err = "ffs_submit_compressed: malformed or unsupported bitshuffle-LZ4 chunk";
+        return rc;
+    }
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    cudaStream_t st = c->streams[s.stream];
+    FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, chunk, chunk_bytes,
+                              cudaMemcpyHostToDevice, st));
+    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->max_blocks,
+                              c->h_blocks + (size_t)slot * c->max_blocks, sizeof(uint2) * a.n_blocks,
+                              cudaMemcpyHostToDevice, st));
+    rc = bslz4_launch(c, slot, a, st);
+    if (rc) return rc;
+    FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + slot, sizeof(unsigned),
+                              cudaMemcpyDeviceToHost, st));
+    s.compressed = true;
+    return submit_tail(c, slot, frame_id, st);
+}
+
+extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, size_t chunk_bytes,
+                                       void* frame_out) {
+    if (!slots_ok(c, slot, 1) || !chunk) return FFS_ERR_ARG;
+    std::unique_lock<std::mutex> lk(c->mu);
+    int rc = bslz4_setup(c);
+    if (rc) return rc;
+    if (chunk_bytes > c->chunk_cap) return FFS_ERR_FORMAT;
+    uint8_t* h = c->h_chunks + (size_t)slot * c->chunk_cap;
+    memcpy(h, chunk, chunk_bytes);
+    Bslz4Args a{};
+    rc = bslz4_index(c, slot, h, chunk_bytes, a);
+    if (rc) return rc;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    cudaStream_t st = c->stream;
+    FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, h, chunk_bytes, cudaMemcpyHostToDevice, st));
+    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->max_blocks,
+                              c->h_blocks + (size_t)slot * c->max_blocks, sizeof(uint2) * a.n_blocks,
+                              cudaMemcpyHostToDevice, st));
+    rc = bslz4_launch(c, slot, a, st);
+    if (rc) return rc;
+    unsigned status = 0;
+    FFS_CK(c, cudaMemcpyAsync(&status, c->d_dec_status + slot, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    FFS_CK(c, cudaStreamSynchronize(st));
+    if (status) return FFS_ERR_FORMAT;
+    if (frame_out) {
+        const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+        FFS_CK(c, cudaMemcpy2D(frame_out, row, c->d_frames + (size_t)slot * c->frame_stride, c->pitch, row,
+                               c->p.height, cudaMemcpyDeviceToHost));
+    }
+    return FFS_OK;
+}

@@ -179,6 +179,7 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaSetDevice(c->p.device);
     cudaDeviceSynchronize();
     stream_teardown(c);
+    bslz4_teardown(c);
     cc_teardown(c);
     cudaFree(c->d_mask);
     cudaFree(c->d_valid_bits);

@@ -54,17 +54,10 @@ extern "C" int ffs_acquire(ffs_ctx* c, int* slot, void** pinned_pixels) {
     }
 }
 
-extern "C" int ffs_submit(ffs_ctx* c, int slot, uint64_t frame_id) {
-    if (!slots_ok(c, slot, 1)) return FFS_ERR_ARG;
-    std::unique_lock<std::mutex> lk(c->mu);
+// Everything after the frame is in the slot's pitched device buffer: threshold, connected
+// components, small result D2H, completion event.  Called with c->mu held.
+static int submit_tail(ffs_ctx* c, int slot, uint64_t frame_id, cudaStream_t st) {
     StreamSlot& s = c->slots[slot];
-    if (s.state != 1) return FFS_ERR_STATE;
-    FFS_CK(c, cudaSetDevice(c->p.device));
-    cudaStream_t st = c->streams[s.stream];
-    const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
-    FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
-                                c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
-                                cudaMemcpyHostToDevice, st));
     int rc = threshold_impl(c, slot, 1, st);
     if (rc == FFS_OK) rc = cc_impl(c, slot, 1, st);
     if (rc) return rc;
@@ -78,6 +71,21 @@ extern "C" int ffs_submit(ffs_ctx* c, int slot, uint64_t frame_id) {
     c->inflight.push_back(slot);
     c->cv.notify_all();
     return FFS_OK;
+}
+
+extern "C" int ffs_submit(ffs_ctx* c, int slot, uint64_t frame_id) {
+    if (!slots_ok(c, slot, 1)) return FFS_ERR_ARG;
+    std::unique_lock<std::mutex> lk(c->mu);
+    StreamSlot& s = c->slots[slot];
+    if (s.state != 1) return FFS_ERR_STATE;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    cudaStream_t st = c->streams[s.stream];
+    const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+    FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
+                                c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
+                                cudaMemcpyHostToDevice, st));
+    s.compressed = false;
+    return submit_tail(c, slot, frame_id, st);
 }
 
 extern "C" int ffs_submit_copy(ffs_ctx* c, uint64_t frame_id, const void* pixels) {
@@ -111,6 +119,10 @@ extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, s
     FFS_CK(c, cudaEventSynchronize(s.done));
     const uint32_t* cnt = c->h_frame_counts + (size_t)slot * CNT_N;
     if (result) counts_to_result(cnt, s.frame_id, result);
+    if (s.compressed && c->h_dec_status && c->h_dec_status[slot] != 0) {
+        // malformed bitshuffle-LZ4 input: the frame was not decoded, its result is void
+        if (result) result->status = FFS_ERR_FORMAT;
+    }
     const size_t have = std::min<size_t>(cnt[CNT_COMPONENTS], c->cap_spots);
     if (n_spots) *n_spots = have;
     int rc = FFS_OK;

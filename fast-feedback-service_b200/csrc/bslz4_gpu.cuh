@@ -1,0 +1,272 @@
+// bslz4_gpu.cuh -- bitshuffle-LZ4 chunk decode ON THE DEVICE.
+//
+// The reference decompresses every frame on the host before the upload
+//   bshuf_decompress_lz4(buffer + 12, host_image, px, sizeof(pixel_t), 0)
+// (spotfinder/spotfinder.cc:823-841, h5read/src/read_chunks.cc:21-25) and notes that the
+// decompression should eventually be offloaded.  Here the COMPRESSED chunk crosses PCIe
+// (4-10x fewer bytes than the frame, and the H2D link is the end-to-end roofline) and one
+// warp decodes one bitshuffle block:
+//   1. the block's LZ4 payload is staged in shared memory (coalesced 16-byte loads);
+//   2. the raw LZ4 block is decoded into a second shared buffer: the token / length parse is
+//      warp-uniform, literal and match copies are warp-parallel (word copies through a
+//      funnel shift; run-length matches with offset 1/2/4 become pattern stores; short
+//      overlapping matches are copied as the periodic sequence they denote);
+//   3. the block -- elem_size*8 bit planes of n/8 bytes -- is transposed back to pixels
+//      (8x8 bit-matrix transposes in registers) and written to the pitched device frame the
+//      threshold kernel reads.
+// Stream format: see csrc/cli/bslz4.hpp (host decoder, same restated format).  The host
+// only walks the 4-byte block headers to build the offset table (ffs_submit_compressed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ffsb {
+
+constexpr int kBslz4MaxBlockBytes = 8192;                       // bitshuffle's default target block
+constexpr int kBslz4InBytes = kBslz4MaxBlockBytes + 8192 / 255 + 64 + 32;  // LZ4 worst case + slack
+constexpr int kBslz4SmemPerWarp = ((kBslz4InBytes + 15) / 16 * 16) + kBslz4MaxBlockBytes + 16;
+
+struct Bslz4Args {
+    const uint8_t* chunk;       // device copy of the whole chunk (header + body), 16-byte aligned
+    const uint2* blocks;        // per block: {payload offset in chunk, payload bytes}
+    uint32_t n_blocks;
+    uint32_t block_elems;       // elements per full block (multiple of 8)
+    uint32_t last_elems;        // elements of the last block
+    uint32_t tail_off;          // offset of the raw trailing (n % 8) elements
+    uint32_t tail_elems;
+    uint64_t tail_elem0;        // index of the first trailing element
+    uint8_t* frame;             // pitched destination
+    size_t pitch;
+    uint32_t width;
+    uint32_t elem_size;         // 2 or 4
+    unsigned int* status;       // set to nonzero on malformed input
+};
+
+// 8x8 bit-matrix transpose of the 64-bit value hi:lo (byte r = row r).
+__device__ __forceinline__ void transpose8(uint32_t& lo, uint32_t& hi) {
+    uint32_t t;
+    t = (lo ^ (lo >> 7)) & 0x00AA00AAu;  lo = lo ^ t ^ (t << 7);
+    t = (hi ^ (hi >> 7)) & 0x00AA00AAu;  hi = hi ^ t ^ (t << 7);
+    t = (lo ^ (lo >> 14)) & 0x0000CCCCu; lo = lo ^ t ^ (t << 14);
+    t = (hi ^ (hi >> 14)) & 0x0000CCCCu; hi = hi ^ t ^ (t << 14);
+    // x ^ (x >> 28) masked with 0x00000000F0F0F0F0: only the low word of t is non-zero
+    t = (lo ^ ((lo >> 28) | (hi << 4))) & 0xF0F0F0F0u;
+    lo = lo ^ t ^ (t << 28);
+    hi = hi ^ (t >> 4);
+}
+
+// Warp-parallel copy of len bytes inside shared memory, dst and src non-overlapping within
+// any 132-byte window (see the caller).  Word stores; the source is realigned with a
+// funnel shift.  Both buffers are padded so that reading one word past the end is safe.
+template <bool SYNC_EACH_ROUND>
+__device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, int len, int lane) {
+    const int head = min((int)((4u - ((uint32_t)__cvta_generic_to_shared(dst) & 3u)) & 3u), len);
+    if (lane < head) dst[lane] = src[lane];
+    const int nwords = (len - head) >> 2;
+    const uint8_t* s = src + head;
+    const uint32_t sh = ((uint32_t)__cvta_generic_to_shared(s) & 3u) * 8u;
+    const uint32_t* sa = reinterpret_cast<const uint32_t*>(s - (sh >> 3));
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst + head);
+    if (SYNC_EACH_ROUND) __syncwarp();
+    for (int base = 0; base < nwords; base += 32) {  // uniform trip count
+        const int w = base + lane;
+        if (w < nwords) d[w] = __funnelshift_r(sa[w], sa[w + 1], sh);
+        // a match with offset >= 132 may read what the previous round wrote
+        if (SYNC_EACH_ROUND) __syncwarp();
+    }
+    const int done = head + (nwords << 2);
+    if (lane < len - done) dst[done + lane] = src[done + lane];
+}
+
+// Decode one raw LZ4 block from in[0..in_len) to out[0..out_len).  Returns false on
+// malformed input.  All lanes take the same path.
+__device__ __forceinline__ bool lz4_warp_decode(const uint8_t* in, int in_len, uint8_t* out, int out_len,
+                                                int lane) {
+    int ip = 0, op = 0;
+    // length extension bytes: 255, 255, ..., b < 255
+    auto extend = [&](int& len) -> bool {
+        for (;;) {
+            const int idx = ip + lane;
+            const uint32_t b = idx < in_len ? in[idx] : 0u;
+            const unsigned nz = __ballot_sync(0xffffffffu, b != 255u);
+            if (nz) {
+                const int first = __ffs(nz) - 1;
+                if (ip + first >= in_len) return false;
+                len += 255 * first + (int)__shfl_sync(0xffffffffu, b, first);
+                ip += first + 1;
+                return true;
+            }
+            len += 255 * 32;
+            ip += 32;
+            if (ip >= in_len) return false;
+        }
+    };
+    while (ip < in_len) {
+        const uint32_t token = in[ip++];
+        int lit = token >> 4;
+        if (lit == 15 && !extend(lit)) return false;
+        if (lit > in_len - ip || lit > out_len - op) return false;
+        if (lit) warp_copy<false>(out + op, in + ip, lit, lane);
+        ip += lit;
+        op += lit;
+        if (ip >= in_len) break;  // the last sequence has no match
+        if (in_len - ip < 2) return false;
+        const int offset = in[ip] | (in[ip + 1] << 8);
+        ip += 2;
+        int mlen = token & 15;
+        if (mlen == 15 && !extend(mlen)) return false;
+        mlen += 4;
+        if (offset == 0 || offset > op || mlen > out_len - op) return false;
+        __syncwarp();  // literals just written may be the match source
+        uint8_t* dst = out + op;
+        if (offset >= mlen) {
+            warp_copy<false>(dst, dst - offset, mlen, lane);
+        } else if (offset >= 132) {
+            warp_copy<true>(dst, dst - offset, mlen, lane);
+        } else if (offset == 1 || offset == 2 || offset == 4) {
+            // run: the 4-byte pattern seen from an aligned word is the same for every word
+            const uint32_t a0 = (uint32_t)__cvta_generic_to_shared(out);  // 16-byte aligned base
+            uint32_t pat = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int p = (int)(((uint32_t)j - (uint32_t)op - a0) & (uint32_t)(offset - 1));
+                pat |= (uint32_t)dst[p - offset] << (8 * j);
+            }
+            const int head = min((int)((16u - ((a0 + (uint32_t)op) & 15u)) & 15u), mlen);
+            if (lane < head) dst[lane] = (uint8_t)(pat >> (8 * ((a0 + op + lane) & 3u)));
+            const int nq = (mlen - head) >> 4;
+            uint4* d = reinterpret_cast<uint4*>(dst + head);
+            const uint4 p4 = make_uint4(pat, pat, pat, pat);
+            for (int w = lane; w < nq; w += 32) d[w] = p4;
+            const int done = head + (nq << 4);
+            if (lane < mlen - done) dst[done + lane] = (uint8_t)(pat >> (8 * ((a0 + op + done + lane) & 3u)));
+        } else {
+            // short overlapping match = periodic sequence with period `offset`
+            const int step = 32 % offset;
+            int km = lane % offset;
+            for (int k = lane; k < mlen; k += 32) {
+                dst[k] = dst[km - offset];
+                km += step;
+                if (km >= offset) km -= offset;
+            }
+        }
+        op += mlen;
+        __syncwarp();
+    }
+    return op == out_len;
+}
+
+// grid: ceil(n_blocks / WARPS) CTAs of WARPS warps; dynamic smem WARPS * kBslz4SmemPerWarp.
+template <typename PixelT, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Args a) {
+    extern __shared__ __align__(16) uint8_t bsmem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t b = blockIdx.x * WARPS + warp;
+    constexpr int ES = (int)sizeof(PixelT);
+    constexpr int IN_CAP = (kBslz4InBytes + 15) / 16 * 16;
+    uint8_t* in = bsmem + (size_t)warp * kBslz4SmemPerWarp;
+    uint8_t* out = in + IN_CAP;
+
+    // raw trailing elements (n % 8), copied by the first thread block
+    if (blockIdx.x == 0 && threadIdx.x < a.tail_elems) {
+        const uint64_t e = a.tail_elem0 + threadIdx.x;
+        const uint8_t* p = a.chunk + a.tail_off + (size_t)threadIdx.x * ES;
+        uint32_t val = 0;
+        for (int k = 0; k < ES; ++k) val |= (uint32_t)p[k] << (8 * k);
+        const PixelT v = (PixelT)val;
+        const uint32_t row = (uint32_t)(e / a.width), col = (uint32_t)(e % a.width);
+        reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
+    }
+    if (b >= a.n_blocks) return;
+    const uint2 blk = a.blocks[b];
+    const int n_el = (b + 1 == a.n_blocks) ? (int)a.last_elems : (int)a.block_elems;
+    const int out_len = n_el * ES;
+    const int in_len = (int)blk.y;
+    if (in_len > kBslz4InBytes - 32 || out_len > kBslz4MaxBlockBytes) {
+        if (lane == 0) atomicExch(a.status, 1u);
+        return;
+    }
+    // 1. stage the payload: 16-byte loads from the aligned address below its start
+    {
+        const uint32_t mis = blk.x & 15u;
+        const uint4* src = reinterpret_cast<const uint4*>(a.chunk + (blk.x - mis));
+        const int nq = (int)((mis + in_len + 15) >> 4);
+        uint4* dstq = reinterpret_cast<uint4*>(in);
+        for (int q = lane; q < nq; q += 32) dstq[q] = src[q];
+        in += mis;
+    }
+    __syncwarp();
+    // 2. LZ4
+    if (!lz4_warp_decode(in, in_len, out, out_len, lane)) {
+        if (lane == 0) atomicExch(a.status, 2u);
+        return;
+    }
+    __syncwarp();
+    // 3. bit planes -> pixels.  Plane (byte j, bit k) is row 8j+k, n_el/8 bytes per row;
+    //    column c holds bit (e & 7) of elements e = 8c .. 8c+7.
+    const int row_bytes = n_el >> 3;
+    const uint64_t e0 = (uint64_t)b * a.block_elems;
+    const bool aligned4 = (a.width & 3u) == 0;
+    for (int c = lane; c < row_bytes; c += 32) {
+        uint32_t w[2 * ES];  // per byte j of the element: 8 output bytes (element i -> byte i)
+#pragma unroll
+        for (int j = 0; j < ES; ++j) {
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                lo |= (uint32_t)out[(8 * j + k) * row_bytes + c] << (8 * k);
+                hi |= (uint32_t)out[(8 * j + 4 + k) * row_bytes + c] << (8 * k);
+            }
+            if (lo | hi) transpose8(lo, hi);
+            w[2 * j] = lo;
+            w[2 * j + 1] = hi;
+        }
+        // interleave: pixel i = bytes (w[0..1] byte i, w[2..3] byte i, ...)
+        uint32_t px[2 * ES];  // 8 pixels * ES bytes
+        if constexpr (ES == 2) {
+            px[0] = __byte_perm(w[0], w[2], 0x5140);  // pixels 0,1
+            px[1] = __byte_perm(w[0], w[2], 0x7362);  // pixels 2,3
+            px[2] = __byte_perm(w[1], w[3], 0x5140);  // pixels 4,5
+            px[3] = __byte_perm(w[1], w[3], 0x7362);  // pixels 6,7
+        } else {
+            // pixel i = b0[i] | b1[i] << 8 | b2[i] << 16 | b3[i] << 24
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t t01a = __byte_perm(w[0 + h], w[2 + h], 0x5140);  // b0[0] b1[0] b0[1] b1[1]
+                const uint32_t t01b = __byte_perm(w[0 + h], w[2 + h], 0x7362);  // b0[2] b1[2] b0[3] b1[3]
+                const uint32_t t23a = __byte_perm(w[4 + h], w[6 + h], 0x5140);
+                const uint32_t t23b = __byte_perm(w[4 + h], w[6 + h], 0x7362);
+                px[4 * h + 0] = __byte_perm(t01a, t23a, 0x5410);
+                px[4 * h + 1] = __byte_perm(t01a, t23a, 0x7632);
+                px[4 * h + 2] = __byte_perm(t01b, t23b, 0x5410);
+                px[4 * h + 3] = __byte_perm(t01b, t23b, 0x7632);
+            }
+        }
+        const uint64_t e = e0 + 8ull * (uint32_t)c;
+        if (aligned4) {
+            // width % 4 == 0: each half (4 pixels) lies in one row and is 4*ES-byte aligned
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint64_t eh = e + 4 * h;
+                const uint32_t row = (uint32_t)(eh / a.width), col = (uint32_t)(eh % a.width);
+                uint8_t* dstp = a.frame + (size_t)row * a.pitch + (size_t)col * ES;
+                if constexpr (ES == 2)
+                    *reinterpret_cast<uint2*>(dstp) = make_uint2(px[2 * h], px[2 * h + 1]);
+                else
+                    *reinterpret_cast<uint4*>(dstp) = make_uint4(px[4 * h], px[4 * h + 1], px[4 * h + 2], px[4 * h + 3]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint64_t ei = e + i;
+                const uint32_t row = (uint32_t)(ei / a.width), col = (uint32_t)(ei % a.width);
+                PixelT v;
+                if constexpr (ES == 2) v = (PixelT)(px[i >> 1] >> (16 * (i & 1)));
+                else v = (PixelT)px[i];
+                reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
+            }
+        }
+    }
+}
+
+}  // namespace ffsb

@@ -28,6 +28,7 @@ struct StreamSlot {
     uint64_t frame_id = 0;
     int state = 0;               // 0 free, 1 acquired (host filling), 2 in flight
     int stream = 0;
+    bool compressed = false;     // submitted through ffs_submit_compressed
 };
 
 }  // namespace ffsb
@@ -76,6 +77,16 @@ struct ffs_ctx {
     uint32_t* h_frame_counts = nullptr;  // n_slots * 8
     ffs_spot* h_spots = nullptr;         // n_slots * cap_spots
     uint8_t* h_frames = nullptr;         // n_slots dense pinned frames
+
+    // compressed ingestion (bslz4_gpu.cuh), allocated on first use
+    size_t chunk_cap = 0;             // bytes per slot
+    uint32_t max_blocks = 0;
+    uint8_t* h_chunks = nullptr;      // pinned, n_slots * chunk_cap
+    uint8_t* d_chunks = nullptr;
+    uint2* h_blocks = nullptr;        // pinned, n_slots * max_blocks {offset, length}
+    uint2* d_blocks = nullptr;
+    unsigned int* d_dec_status = nullptr;  // n_slots
+    unsigned int* h_dec_status = nullptr;  // pinned
 
     // TMA descriptors
     CUtensorMap tm_img{};     // 3D: x, y, slot

@@ -7,6 +7,7 @@
 #include "extended.cuh"
 #include "cc.cuh"
 #include "cc3d.cuh"
+#include "bslz4_gpu.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -84,11 +85,13 @@ static int cc_setup(ffs_ctx* c);
 static void cc_teardown(ffs_ctx* c);
 static int stream_setup(ffs_ctx* c);
 static void stream_teardown(ffs_ctx* c);
+static void bslz4_teardown(ffs_ctx* c);
 static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_strong);
 
 #include "api_core.inl"
 #include "api_ext.inl"
 #include "api_cc.inl"
 #include "api_stream.inl"
+#include "api_bslz4.inl"
 #include "api_sweep.inl"
 #include "api_shim.inl"

@@ -206,6 +206,26 @@ class Spotfinder:
             raise ValueError("frame shape must be (height, width)")
         self._ck(self._L.ffs_submit_copy(self._ctx, frame_id, f.ctypes.data), "ffs_submit_copy")
 
+    # -- compressed ingestion: bitshuffle-LZ4 chunk decoded on the device ------------------------
+    def acquire_compressed(self):
+        """(slot, uint8 view of the slot's pinned chunk buffer) -- fill it with the raw HDF5
+        filter chunk (12-byte header + body), then submit_compressed(slot, id, n_bytes)."""
+        slot, ptr, cap = C.c_int(-1), C.c_void_p(), C.c_size_t(0)
+        self._ck(self._L.ffs_acquire_compressed(self._ctx, C.byref(slot), C.byref(ptr), C.byref(cap)),
+                 "ffs_acquire_compressed")
+        buf = (C.c_uint8 * cap.value).from_address(ptr.value)
+        return slot.value, np.frombuffer(buf, dtype=np.uint8)
+
+    def submit_compressed(self, slot: int, frame_id: int, n_bytes: int):
+        self._ck(self._L.ffs_submit_compressed(self._ctx, slot, frame_id, n_bytes), "ffs_submit_compressed")
+
+    def decode_chunk(self, chunk: bytes, slot: int = 0) -> np.ndarray:
+        """Parity hook: decode one chunk on the device and return the dense frame."""
+        out = np.empty((self.height, self.width), self.dtype)
+        self._ck(self._L.ffs_decode_chunk_device(self._ctx, slot, chunk, len(chunk), out.ctypes.data),
+                 "ffs_decode_chunk_device")
+        return out
+
     @property
     def pending(self) -> int:
         return self._L.ffs_pending(self._ctx)

@@ -56,7 +56,8 @@ typedef enum ffs_status {
     FFS_ERR_NO_DEVICE = -3,/* no CUDA device / wrong architecture              */
     FFS_ERR_CAPACITY = -4, /* a per-frame capacity (strong pixels, spots) hit  */
     FFS_ERR_STATE = -5,    /* call sequence error (slot busy, nothing pending) */
-    FFS_ERR_NOMEM = -6
+    FFS_ERR_NOMEM = -6,
+    FFS_ERR_FORMAT = -7,   /* malformed / unsupported compressed chunk          */
 } ffs_status;
 
 typedef struct ffs_ctx ffs_ctx;
@@ -174,6 +175,23 @@ int ffs_submit_copy(ffs_ctx *ctx, uint64_t frame_id, const void *pixels);
 int ffs_wait(ffs_ctx *ctx, ffs_frame_result *result, ffs_spot *spots, size_t max_spots,
              size_t *n_spots);
 int ffs_pending(ffs_ctx *ctx);
+
+/* ---- compressed ingestion: bitshuffle-LZ4 decoded on the device ------------------------------
+ * Replaces the host-side bshuf_decompress_lz4(buffer + 12, host_image, px, sizeof(pixel_t), 0)
+ * + cudaMemcpy2DAsync of the dense frame (spotfinder/spotfinder.cc:823-846): the raw HDF5
+ * filter chunk (12-byte header + body, exactly what Reader::get_raw_chunk returns,
+ * h5read.h:173-204) is uploaded as it is and decoded by bslz4_decode_kernel, so 4-10x fewer
+ * bytes cross the H2D link.  ffs_acquire_compressed returns the slot's pinned chunk buffer
+ * and its capacity; ffs_submit_compressed walks the 4-byte block headers on the host (the
+ * only serial step), queues H2D + decode + the same kernels as ffs_submit.  Results arrive
+ * through ffs_wait; a malformed chunk gives result.status == FFS_ERR_FORMAT.
+ * Supported: elem size = bytes_per_pixel, block size <= 8192 bytes (bitshuffle's default). */
+int ffs_acquire_compressed(ffs_ctx *ctx, int *slot, void **pinned_chunk, size_t *capacity);
+int ffs_submit_compressed(ffs_ctx *ctx, int slot, uint64_t frame_id, size_t chunk_bytes);
+/* Parity hook: decode a chunk into device slot `slot` (no further processing) and copy the
+ * dense frame back to host memory. */
+int ffs_decode_chunk_device(ffs_ctx *ctx, int slot, const void *chunk, size_t chunk_bytes,
+                            void *frame_out);
 
 /* ---- rotation sweeps: 3D connected components (find_3d_components) ---------------------- */
 /* Frames processed with sweep recording on keep their strong-pixel lists on the device;

@@ -45,3 +45,24 @@ def test_corrupt_input_is_rejected():
     bad = bytearray(chunk)
     bad[12:16] = b"\xff\xff\xff\xff"                           # absurd block length
     assert decode(bytes(bad), a.size, np.uint16)[0] != 0
+
+
+def test_lz4_blocks_pinned_against_liblz4():
+    """The LZ4 block format is pinned against the real liblz4 (pyarrow's lz4_raw codec): it
+    decodes what the test encoder emits, and the product's host decoder decodes what liblz4
+    emits (chunks built by ffs_b200.bslz4_encode)."""
+    pa = pytest.importorskip("pyarrow")
+    from bslz4_ref import _lz4_block
+    from ffs_b200 import bslz4_encode
+    codec = pa.Codec("lz4_raw")
+    rng = np.random.default_rng(5)
+    for data in (bytes(5000), rng.integers(0, 4, 3000).astype(np.uint8).tobytes(),
+                 rng.integers(0, 256, 2000).astype(np.uint8).tobytes(), b"abcabcabc" * 300):
+        assert codec.decompress(_lz4_block(data), decompressed_size=len(data), asbytes=True) == data
+    for dtype in (np.uint16, np.uint32):
+        for n in (8, 4100, 9001, 70 * 90):
+            a = rng.poisson(3.0, n).astype(dtype)
+            chunk = bslz4_encode.compress_chunk(a)
+            assert chunk[:12] == compress_chunk(a)[:12]
+            rc, out = decode(chunk, n, dtype)
+            assert rc == 0 and np.array_equal(out, a)
