@@ -19,8 +19,9 @@ static int bslz4_setup(ffs_ctx* c) {
     FFS_CK(c, cudaSetDevice(c->p.device));
     FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_cap * S, cudaHostAllocDefault));
     FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_cap * S + 64));
-    FFS_CK(c, cudaHostAlloc(&c->h_blocks, sizeof(uint2) * c->max_blocks * S, cudaHostAllocDefault));
-    FFS_CK(c, cudaMalloc(&c->d_blocks, sizeof(uint2) * c->max_blocks * S));
+    c->blocks_stride = sizeof(Bslz4Dyn) + sizeof(uint2) * c->max_blocks;
+    FFS_CK(c, cudaHostAlloc(&c->h_blocks, c->blocks_stride * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaMalloc(&c->d_blocks, c->blocks_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_dec_status, sizeof(unsigned) * S));
     FFS_CK(c, cudaHostAlloc(&c->h_dec_status, sizeof(unsigned) * S, cudaHostAllocDefault));
     memset(c->h_dec_status, 0, sizeof(unsigned) * S);
@@ -37,7 +38,7 @@ static void bslz4_teardown(ffs_ctx* c) {
 }
 
 // Walk the block headers of `chunk` (host memory) and fill the slot's block table.
-static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, Bslz4Args& a) {
+static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, Bslz4Dyn& a) {
     const size_t es = c->p.bytes_per_pixel;
     const size_t n = (size_t)c->p.width * c->p.height;
     if (len < 12 || len > c->chunk_cap) return FFS_ERR_FORMAT;
@@ -51,7 +52,8 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
     last -= last % 8;
     const size_t n_blocks = full + (last ? 1 : 0);
     if (n_blocks > c->max_blocks) return FFS_ERR_FORMAT;
-    uint2* tab = c->h_blocks + (size_t)slot * c->max_blocks;
+    Bslz4Dyn* hdr = reinterpret_cast<Bslz4Dyn*>(c->h_blocks + (size_t)slot * c->blocks_stride);
+    uint2* tab = reinterpret_cast<uint2*>(hdr + 1);
     size_t pos = 12;
     for (size_t b = 0; b < n_blocks; ++b) {
         if (len - pos < 4) return FFS_ERR_FORMAT;
@@ -68,21 +70,25 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
     a.last_elems = (uint32_t)(last ? last : block);
     a.tail_off = (uint32_t)pos;
     a.tail_elems = (uint32_t)tail;
-    a.tail_elem0 = (uint64_t)(n - tail);
+    a.tail_elem0 = (uint32_t)(n - tail);
+    a.pad[0] = a.pad[1] = 0;
+    *hdr = a;
     return FFS_OK;
 }
 
-static int bslz4_launch(ffs_ctx* c, int slot, Bslz4Args& a, cudaStream_t st) {
-    constexpr int kWarps = 4;
+static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st) {
+    constexpr int kWarps = 2;
+    Bslz4Args a{};
     a.chunk = c->d_chunks + (size_t)slot * c->chunk_cap;
-    a.blocks = c->d_blocks + (size_t)slot * c->max_blocks;
+    a.dyn = reinterpret_cast<const Bslz4Dyn*>(c->d_blocks + (size_t)slot * c->blocks_stride);
     a.frame = c->d_frames + (size_t)slot * c->frame_stride;
     a.pitch = c->pitch;
     a.width = c->p.width;
     a.elem_size = c->p.bytes_per_pixel;
+    a.inv_width = (uint32_t)((1ull << 32) / c->p.width) + 1u;
     a.status = c->d_dec_status + slot;
     const int smem = kWarps * kBslz4SmemPerWarp;
-    const unsigned grid = std::max(1u, (a.n_blocks + kWarps - 1) / kWarps);
+    const unsigned grid = std::max(1u, (n_blocks + kWarps - 1) / kWarps);
     static bool attr_done[64][2] = {};
     const int pi = c->p.bytes_per_pixel == 2 ? 0 : 1;
     if (!attr_done[c->p.device & 63][pi]) {
@@ -119,31 +125,47 @@ extern "C" int ffs_acquire_compressed(ffs_ctx* c, int* slot, void** pinned_chunk
     return FFS_OK;
 }
 
+extern "C" int ffs_slot_buffers(ffs_ctx* c, int slot, void** pinned_pixels, void** pinned_chunk,
+                                size_t* chunk_capacity) {
+    if (!slots_ok(c, slot, 1)) return FFS_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (pinned_chunk || chunk_capacity) {
+        int rc = bslz4_setup(c);
+        if (rc) return rc;
+    }
+    if (pinned_pixels)
+        *pinned_pixels = c->h_frames + (size_t)slot * ((size_t)c->p.width * c->p.height * c->p.bytes_per_pixel);
+    if (pinned_chunk) *pinned_chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
+    if (chunk_capacity) *chunk_capacity = c->chunk_cap;
+    return FFS_OK;
+}
+
 extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, size_t chunk_bytes) {
     if (!slots_ok(c, slot, 1) || !c->h_chunks) return FFS_ERR_ARG;
+    // The header walk (one dependent, usually cache-missing read per block: ~75 ns each when
+    // the chunk was DMA-ed into the buffer rather than written by this core) runs outside the
+    // context lock: the slot belongs to the caller until it is submitted, so producer threads
+    // index their chunks in parallel.
+    const uint8_t* chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
+    Bslz4Dyn dyn{};
+    int rc = bslz4_index(c, slot, chunk, chunk_bytes, dyn);
     std::unique_lock<std::mutex> lk(c->mu);
     StreamSlot& s = c->slots[slot];
     if (s.state != 1) return FFS_ERR_STATE;
-    const uint8_t* chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
-    Bslz4Args a{};
-    int rc = bslz4_index(c, slot, chunk, chunk_bytes, a);
     if (rc) {
         c->err = "ffs_submit_compressed: malformed or unsupported bitshuffle-LZ4 chunk";
         return rc;
     }
     FFS_CK(c, cudaSetDevice(c->p.device));
     cudaStream_t st = c->streams[s.stream];
+    // the two uploads whose sizes change from frame to frame stay outside the slot's graph
     FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, chunk, chunk_bytes,
                               cudaMemcpyHostToDevice, st));
-    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->max_blocks,
-                              c->h_blocks + (size_t)slot * c->max_blocks, sizeof(uint2) * a.n_blocks,
-                              cudaMemcpyHostToDevice, st));
-    rc = bslz4_launch(c, slot, a, st);
-    if (rc) return rc;
-    FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + slot, sizeof(unsigned),
-                              cudaMemcpyDeviceToHost, st));
+    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
+                              c->h_blocks + (size_t)slot * c->blocks_stride,
+                              sizeof(Bslz4Dyn) + sizeof(uint2) * dyn.n_blocks, cudaMemcpyHostToDevice, st));
     s.compressed = true;
-    return submit_tail(c, slot, frame_id, st);
+    return submit_tail(c, slot, 1, dyn.n_blocks, frame_id, st);
 }
 
 extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, size_t chunk_bytes,
@@ -155,16 +177,16 @@ extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, 
     if (chunk_bytes > c->chunk_cap) return FFS_ERR_FORMAT;
     uint8_t* h = c->h_chunks + (size_t)slot * c->chunk_cap;
     memcpy(h, chunk, chunk_bytes);
-    Bslz4Args a{};
-    rc = bslz4_index(c, slot, h, chunk_bytes, a);
+    Bslz4Dyn dyn{};
+    rc = bslz4_index(c, slot, h, chunk_bytes, dyn);
     if (rc) return rc;
     FFS_CK(c, cudaSetDevice(c->p.device));
     cudaStream_t st = c->stream;
     FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, h, chunk_bytes, cudaMemcpyHostToDevice, st));
-    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->max_blocks,
-                              c->h_blocks + (size_t)slot * c->max_blocks, sizeof(uint2) * a.n_blocks,
-                              cudaMemcpyHostToDevice, st));
-    rc = bslz4_launch(c, slot, a, st);
+    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
+                              c->h_blocks + (size_t)slot * c->blocks_stride,
+                              sizeof(Bslz4Dyn) + sizeof(uint2) * dyn.n_blocks, cudaMemcpyHostToDevice, st));
+    rc = bslz4_launch(c, slot, dyn.n_blocks, st);
     if (rc) return rc;
     unsigned status = 0;
     FFS_CK(c, cudaMemcpyAsync(&status, c->d_dec_status + slot, sizeof(unsigned), cudaMemcpyDeviceToHost, st));

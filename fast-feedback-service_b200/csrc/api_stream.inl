@@ -22,8 +22,11 @@ static int stream_setup(ffs_ctx* c) {
 }
 
 static void stream_teardown(ffs_ctx* c) {
-    for (auto& s : c->slots)
+    for (auto& s : c->slots) {
         if (s.done) cudaEventDestroy(s.done);
+        for (auto& g : s.graph)
+            if (g) cudaGraphExecDestroy(g);
+    }
     for (auto& s : c->streams)
         if (s) cudaStreamDestroy(s);
     cudaFreeHost(c->h_frames);
@@ -54,10 +57,23 @@ extern "C" int ffs_acquire(ffs_ctx* c, int* slot, void** pinned_pixels) {
     }
 }
 
-// Everything after the frame is in the slot's pitched device buffer: threshold, connected
-// components, small result D2H, completion event.  Called with c->mu held.
-static int submit_tail(ffs_ctx* c, int slot, uint64_t frame_id, cudaStream_t st) {
-    StreamSlot& s = c->slots[slot];
+static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st);
+
+// The device work of one frame in ring slot `slot`, queued on st.  mode 0: H2D of the dense
+// pinned frame; mode 1: decode of the (already uploaded) compressed chunk.  Then threshold,
+// connected components and the small result D2H.
+static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStream_t st) {
+    if (mode == 0) {
+        const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+        FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
+                                    c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
+                                    cudaMemcpyHostToDevice, st));
+    } else {
+        int rc = bslz4_launch(c, slot, n_blocks, st);
+        if (rc) return rc;
+        FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + slot, sizeof(unsigned),
+                                  cudaMemcpyDeviceToHost, st));
+    }
     int rc = threshold_impl(c, slot, 1, st);
     if (rc == FFS_OK) rc = cc_impl(c, slot, 1, st);
     if (rc) return rc;
@@ -65,6 +81,48 @@ static int submit_tail(ffs_ctx* c, int slot, uint64_t frame_id, cudaStream_t st)
                               sizeof(uint32_t) * CNT_N, cudaMemcpyDeviceToHost, st));
     FFS_CK(c, cudaMemcpyAsync(c->h_spots + (size_t)slot * kAsyncSpots, c->d_spots + (size_t)slot * c->cap_spots,
                               sizeof(ffs_spot) * std::min(kAsyncSpots, c->cap_spots), cudaMemcpyDeviceToHost, st));
+    return FFS_OK;
+}
+
+// Queue one frame.  The launch sequence of a slot never changes (same buffers, same launch
+// parameters), so from its second use on it is captured into a CUDA graph and replayed with
+// one cudaGraphLaunch instead of ~20 runtime calls: the per-frame host cost is what bounds
+// small-frame / compressed-ingest rates (FFS_GRAPH=0 disables).  Called with c->mu held.
+static int submit_tail(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, uint64_t frame_id, cudaStream_t st) {
+    StreamSlot& s = c->slots[slot];
+    static const int use_graph = env_int("FFS_GRAPH", 1);
+    const bool graph_ok = use_graph && !c->prof_on && s.uses[mode] >= 1;
+    if (graph_ok && s.graph[mode] && mode == 1 && s.graph_blocks != n_blocks) {
+        cudaGraphExecDestroy(s.graph[mode]);  // block size changed: rebuild
+        s.graph[mode] = nullptr;
+    }
+    if (graph_ok && !s.graph[mode]) {
+        const uint64_t before = c->launches.load();
+        cudaGraph_t g = nullptr;
+        FFS_CK(c, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = slot_work(c, slot, mode, n_blocks, st);
+        cudaError_t e = cudaStreamEndCapture(st, &g);
+        const uint64_t after = c->launches.load();
+        c->launches -= (after - before);  // nothing ran during capture
+        if (rc) {
+            if (g) cudaGraphDestroy(g);
+            return rc;
+        }
+        FFS_CK(c, e);
+        e = cudaGraphInstantiate(&s.graph[mode], g, 0);
+        cudaGraphDestroy(g);
+        FFS_CK(c, e);
+        s.graph_kernels[mode] = (uint32_t)(after - before);
+        s.graph_blocks = n_blocks;
+    }
+    if (graph_ok) {
+        FFS_CK(c, cudaGraphLaunch(s.graph[mode], st));
+        c->launches += s.graph_kernels[mode];
+    } else {
+        int rc = slot_work(c, slot, mode, n_blocks, st);
+        if (rc) return rc;
+    }
+    s.uses[mode]++;
     FFS_CK(c, cudaEventRecord(s.done, st));
     s.frame_id = frame_id;
     s.state = 2;
@@ -80,12 +138,8 @@ extern "C" int ffs_submit(ffs_ctx* c, int slot, uint64_t frame_id) {
     if (s.state != 1) return FFS_ERR_STATE;
     FFS_CK(c, cudaSetDevice(c->p.device));
     cudaStream_t st = c->streams[s.stream];
-    const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
-    FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
-                                c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
-                                cudaMemcpyHostToDevice, st));
     s.compressed = false;
-    return submit_tail(c, slot, frame_id, st);
+    return submit_tail(c, slot, 0, 0, frame_id, st);
 }
 
 extern "C" int ffs_submit_copy(ffs_ctx* c, uint64_t frame_id, const void* pixels) {

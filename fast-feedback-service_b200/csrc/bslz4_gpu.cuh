@@ -6,8 +6,8 @@
 // decompression should eventually be offloaded.  Here the COMPRESSED chunk crosses PCIe
 // (4-10x fewer bytes than the frame, and the H2D link is the end-to-end roofline) and one
 // warp decodes one bitshuffle block:
-//   1. the block's LZ4 payload is staged in shared memory (coalesced 16-byte loads);
-//   2. the raw LZ4 block is decoded into a second shared buffer: the token / length parse is
+//   1. (the compressed payload is read in place: global memory through L1)
+//   2. the raw LZ4 block is decoded into a shared buffer: the token / length parse is
 //      warp-uniform, literal and match copies are warp-parallel (word copies through a
 //      funnel shift; run-length matches with offset 1/2/4 become pattern stores; short
 //      overlapping matches are copied as the periodic sequence they denote);
@@ -24,21 +24,29 @@ namespace ffsb {
 
 constexpr int kBslz4MaxBlockBytes = 8192;                       // bitshuffle's default target block
 constexpr int kBslz4InBytes = kBslz4MaxBlockBytes + 8192 / 255 + 64 + 32;  // LZ4 worst case + slack
-constexpr int kBslz4SmemPerWarp = ((kBslz4InBytes + 15) / 16 * 16) + kBslz4MaxBlockBytes + 16;
+constexpr int kBslz4SmemPerWarp = kBslz4MaxBlockBytes + 16;  // the decoded (bit-transposed) block
 
-struct Bslz4Args {
-    const uint8_t* chunk;       // device copy of the whole chunk (header + body), 16-byte aligned
-    const uint2* blocks;        // per block: {payload offset in chunk, payload bytes}
+// Per-frame values live in device memory (uploaded with the block table), so the kernel
+// arguments of a ring slot never change and the slot's work can be replayed as a CUDA graph.
+struct Bslz4Dyn {
     uint32_t n_blocks;
     uint32_t block_elems;       // elements per full block (multiple of 8)
     uint32_t last_elems;        // elements of the last block
     uint32_t tail_off;          // offset of the raw trailing (n % 8) elements
     uint32_t tail_elems;
-    uint64_t tail_elem0;        // index of the first trailing element
+    uint32_t tail_elem0;        // index of the first trailing element
+    uint32_t pad[2];
+};
+static_assert(sizeof(Bslz4Dyn) == 32, "header precedes the uint2 block table");
+
+struct Bslz4Args {
+    const uint8_t* chunk;       // device copy of the whole chunk (header + body), 16-byte aligned
+    const Bslz4Dyn* dyn;        // followed by per block: uint2 {payload offset in chunk, payload bytes}
     uint8_t* frame;             // pitched destination
     size_t pitch;
     uint32_t width;
     uint32_t elem_size;         // 2 or 4
+    uint32_t inv_width;         // floor(2^32 / width) + 1: n / width == umulhi(n, inv_width) for n*width < 2^32
     unsigned int* status;       // set to nonzero on malformed input
 };
 
@@ -55,33 +63,38 @@ __device__ __forceinline__ void transpose8(uint32_t& lo, uint32_t& hi) {
     hi = hi ^ (t >> 4);
 }
 
-// Warp-parallel copy of len bytes inside shared memory, dst and src non-overlapping within
-// any 132-byte window (see the caller).  Word stores; the source is realigned with a
-// funnel shift.  Both buffers are padded so that reading one word past the end is safe.
+// Warp-parallel copy of len bytes to shared memory from shared or global memory.  Word
+// stores; the source is realigned with a funnel shift (it may be read up to 4 bytes past its
+// end: every buffer is padded).  SYNC_EACH_ROUND: the source may have been written by the
+// previous 128-byte round (overlapping match with offset >= 132).
 template <bool SYNC_EACH_ROUND>
 __device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, int len, int lane) {
-    const int head = min((int)((4u - ((uint32_t)__cvta_generic_to_shared(dst) & 3u)) & 3u), len);
+    if (len <= 32) {  // the common case: one masked byte copy
+        if (lane < len) dst[lane] = src[lane];
+        return;
+    }
+    const int head = (int)((4u - ((uint32_t)reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u);
     if (lane < head) dst[lane] = src[lane];
     const int nwords = (len - head) >> 2;
     const uint8_t* s = src + head;
-    const uint32_t sh = ((uint32_t)__cvta_generic_to_shared(s) & 3u) * 8u;
+    const uint32_t sh = ((uint32_t)reinterpret_cast<uintptr_t>(s) & 3u) * 8u;
     const uint32_t* sa = reinterpret_cast<const uint32_t*>(s - (sh >> 3));
     uint32_t* d = reinterpret_cast<uint32_t*>(dst + head);
     if (SYNC_EACH_ROUND) __syncwarp();
     for (int base = 0; base < nwords; base += 32) {  // uniform trip count
         const int w = base + lane;
         if (w < nwords) d[w] = __funnelshift_r(sa[w], sa[w + 1], sh);
-        // a match with offset >= 132 may read what the previous round wrote
         if (SYNC_EACH_ROUND) __syncwarp();
     }
     const int done = head + (nwords << 2);
     if (lane < len - done) dst[done + lane] = src[done + lane];
 }
 
-// Decode one raw LZ4 block from in[0..in_len) to out[0..out_len).  Returns false on
-// malformed input.  All lanes take the same path.
-__device__ __forceinline__ bool lz4_warp_decode(const uint8_t* in, int in_len, uint8_t* out, int out_len,
-                                                int lane) {
+// Decode one raw LZ4 block from in[0..in_len) (global memory, read through L1: the parse is
+// sequential, so every 128-byte line serves many sequences) to out[0..out_len) (shared).
+// Returns false on malformed input.  All lanes take the same path.
+__device__ __forceinline__ bool lz4_warp_decode(const uint8_t* __restrict__ in, int in_len, uint8_t* out,
+                                                int out_len, int lane) {
     int ip = 0, op = 0;
     // length extension bytes: 255, 255, ..., b < 255
     auto extend = [&](int& len) -> bool {
@@ -117,15 +130,13 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* in, int in_len, u
         if (mlen == 15 && !extend(mlen)) return false;
         mlen += 4;
         if (offset == 0 || offset > op || mlen > out_len - op) return false;
-        __syncwarp();  // literals just written may be the match source
+        if (lit) __syncwarp();  // literals just written may be the match source
         uint8_t* dst = out + op;
         if (offset >= mlen) {
             warp_copy<false>(dst, dst - offset, mlen, lane);
-        } else if (offset >= 132) {
-            warp_copy<true>(dst, dst - offset, mlen, lane);
         } else if (offset == 1 || offset == 2 || offset == 4) {
             // run: the 4-byte pattern seen from an aligned word is the same for every word
-            const uint32_t a0 = (uint32_t)__cvta_generic_to_shared(out);  // 16-byte aligned base
+            const uint32_t a0 = (uint32_t)reinterpret_cast<uintptr_t>(out);  // 16-byte aligned base
             uint32_t pat = 0;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -140,6 +151,8 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* in, int in_len, u
             for (int w = lane; w < nq; w += 32) d[w] = p4;
             const int done = head + (nq << 4);
             if (lane < mlen - done) dst[done + lane] = (uint8_t)(pat >> (8 * ((a0 + op + done + lane) & 3u)));
+        } else if (offset >= 132) {
+            warp_copy<true>(dst, dst - offset, mlen, lane);
         } else {
             // short overlapping match = periodic sequence with period `offset`
             const int step = 32 % offset;
@@ -160,42 +173,33 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* in, int in_len, u
 template <typename PixelT, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Args a) {
     extern __shared__ __align__(16) uint8_t bsmem[];
+    const Bslz4Dyn dyn = *a.dyn;
+    const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t b = blockIdx.x * WARPS + warp;
     constexpr int ES = (int)sizeof(PixelT);
-    constexpr int IN_CAP = (kBslz4InBytes + 15) / 16 * 16;
-    uint8_t* in = bsmem + (size_t)warp * kBslz4SmemPerWarp;
-    uint8_t* out = in + IN_CAP;
+    uint8_t* out = bsmem + (size_t)warp * kBslz4SmemPerWarp;
 
     // raw trailing elements (n % 8), copied by the first thread block
-    if (blockIdx.x == 0 && threadIdx.x < a.tail_elems) {
-        const uint64_t e = a.tail_elem0 + threadIdx.x;
-        const uint8_t* p = a.chunk + a.tail_off + (size_t)threadIdx.x * ES;
+    if (blockIdx.x == 0 && threadIdx.x < dyn.tail_elems) {
+        const uint32_t e = dyn.tail_elem0 + threadIdx.x;
+        const uint8_t* p = a.chunk + dyn.tail_off + (size_t)threadIdx.x * ES;
         uint32_t val = 0;
         for (int k = 0; k < ES; ++k) val |= (uint32_t)p[k] << (8 * k);
         const PixelT v = (PixelT)val;
-        const uint32_t row = (uint32_t)(e / a.width), col = (uint32_t)(e % a.width);
+        const uint32_t row = e / a.width, col = e % a.width;
         reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
     }
-    if (b >= a.n_blocks) return;
-    const uint2 blk = a.blocks[b];
-    const int n_el = (b + 1 == a.n_blocks) ? (int)a.last_elems : (int)a.block_elems;
+    if (b >= dyn.n_blocks) return;
+    const uint2 blk = blocks[b];
+    const int n_el = (b + 1 == dyn.n_blocks) ? (int)dyn.last_elems : (int)dyn.block_elems;
     const int out_len = n_el * ES;
     const int in_len = (int)blk.y;
     if (in_len > kBslz4InBytes - 32 || out_len > kBslz4MaxBlockBytes) {
         if (lane == 0) atomicExch(a.status, 1u);
         return;
     }
-    // 1. stage the payload: 16-byte loads from the aligned address below its start
-    {
-        const uint32_t mis = blk.x & 15u;
-        const uint4* src = reinterpret_cast<const uint4*>(a.chunk + (blk.x - mis));
-        const int nq = (int)((mis + in_len + 15) >> 4);
-        uint4* dstq = reinterpret_cast<uint4*>(in);
-        for (int q = lane; q < nq; q += 32) dstq[q] = src[q];
-        in += mis;
-    }
-    __syncwarp();
+    const uint8_t* in = a.chunk + blk.x;
     // 2. LZ4
     if (!lz4_warp_decode(in, in_len, out, out_len, lane)) {
         if (lane == 0) atomicExch(a.status, 2u);
@@ -205,18 +209,36 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
     // 3. bit planes -> pixels.  Plane (byte j, bit k) is row 8j+k, n_el/8 bytes per row;
     //    column c holds bit (e & 7) of elements e = 8c .. 8c+7.
     const int row_bytes = n_el >> 3;
-    const uint64_t e0 = (uint64_t)b * a.block_elems;
+    // 32-bit index arithmetic (frames have < 2^32 pixels); one division per warp
+    const uint32_t e0 = b * dyn.block_elems;
+    const uint32_t row0 = e0 / a.width, col0 = e0 - row0 * a.width;
     const bool aligned4 = (a.width & 3u) == 0;
-    for (int c = lane; c < row_bytes; c += 32) {
+    const uint32_t pitch32 = (uint32_t)a.pitch;  // a device frame is far below 4 GB
+    // A lane takes 4 adjacent columns (32 pixels) per round when the plane rows are word
+    // aligned (16 LDS.32 instead of 64 LDS.U8); ragged last blocks take one column per round.
+    const bool quad = (row_bytes & 3) == 0;
+    const int n_units = quad ? row_bytes >> 2 : row_bytes;
+    for (int unit = lane; unit < n_units; unit += 32) {
+      uint32_t pl[8 * ES];  // plane words: byte q = column 4*unit + q (quad) / byte 0 = column (single)
+#pragma unroll
+      for (int r = 0; r < 8 * ES; ++r)
+          pl[r] = quad ? *reinterpret_cast<const uint32_t*>(out + r * row_bytes + 4 * unit)
+                       : (uint32_t)out[r * row_bytes + unit];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q > 0 && !quad) break;
+        const int c = quad ? 4 * unit + q : unit;
         uint32_t w[2 * ES];  // per byte j of the element: 8 output bytes (element i -> byte i)
 #pragma unroll
         for (int j = 0; j < ES; ++j) {
-            uint32_t lo = 0, hi = 0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                lo |= (uint32_t)out[(8 * j + k) * row_bytes + c] << (8 * k);
-                hi |= (uint32_t)out[(8 * j + 4 + k) * row_bytes + c] << (8 * k);
-            }
+            // gather byte q of planes 8j .. 8j+7
+            const uint32_t sel = 0x4040u + 0x11u * (uint32_t)q;   // {x.bq, y.bq} in the low half
+            const uint32_t a01 = __byte_perm(pl[8 * j + 0], pl[8 * j + 1], sel);
+            const uint32_t a23 = __byte_perm(pl[8 * j + 2], pl[8 * j + 3], sel);
+            const uint32_t a45 = __byte_perm(pl[8 * j + 4], pl[8 * j + 5], sel);
+            const uint32_t a67 = __byte_perm(pl[8 * j + 6], pl[8 * j + 7], sel);
+            uint32_t lo = __byte_perm(a01, a23, 0x5410);
+            uint32_t hi = __byte_perm(a45, a67, 0x5410);
             if (lo | hi) transpose8(lo, hi);
             w[2 * j] = lo;
             w[2 * j + 1] = hi;
@@ -242,14 +264,15 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
                 px[4 * h + 3] = __byte_perm(t01b, t23b, 0x7632);
             }
         }
-        const uint64_t e = e0 + 8ull * (uint32_t)c;
+        const uint32_t eo = col0 + 8u * (uint32_t)c;  // offset from the start of row0
         if (aligned4) {
             // width % 4 == 0: each half (4 pixels) lies in one row and is 4*ES-byte aligned
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const uint64_t eh = e + 4 * h;
-                const uint32_t row = (uint32_t)(eh / a.width), col = (uint32_t)(eh % a.width);
-                uint8_t* dstp = a.frame + (size_t)row * a.pitch + (size_t)col * ES;
+                const uint32_t eh = eo + 4 * h;
+                const uint32_t dr = __umulhi(eh, a.inv_width);  // eh < width + 8192
+                const uint32_t row = row0 + dr, col = eh - dr * a.width;
+                uint8_t* dstp = a.frame + (row * pitch32 + col * ES);
                 if constexpr (ES == 2)
                     *reinterpret_cast<uint2*>(dstp) = make_uint2(px[2 * h], px[2 * h + 1]);
                 else
@@ -258,14 +281,16 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const uint64_t ei = e + i;
-                const uint32_t row = (uint32_t)(ei / a.width), col = (uint32_t)(ei % a.width);
+                const uint32_t ei = eo + i;
+                const uint32_t dr = __umulhi(ei, a.inv_width);
+                const uint32_t row = row0 + dr, col = ei - dr * a.width;
                 PixelT v;
                 if constexpr (ES == 2) v = (PixelT)(px[i >> 1] >> (16 * (i & 1)));
                 else v = (PixelT)px[i];
                 reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
             }
         }
+      }
     }
 }
 

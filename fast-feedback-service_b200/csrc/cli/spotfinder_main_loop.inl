@@ -40,6 +40,7 @@
     const auto all_images_start = clk::now();
     printf("Finding spots in %u images (%u x %u) with %u threads\n", num_images, width, height, args.threads);
 
+    const bool host_decode = getenv("FFS_HOST_DECODE") && atoi(getenv("FFS_HOST_DECODE")) != 0;
     auto worker = [&](int thread_id) {
         std::vector<uint8_t> chunk, scratch;
         while (!g_stop) {
@@ -75,14 +76,27 @@
             int slot = -1;
             void* pinned = nullptr;
             if (ffs_acquire(ctx, &slot, &pinned) != FFS_OK) break;
-            // decompress straight into the pinned ring slot (no intermediate host copy)
-            if (bslz4::decompress_chunk(chunk.data(), chunk.size(), pinned, px, sizeof(pixel_t), scratch) != 0) {
-                printf("Error: could not decompress image %zu\n", offset_image_num);
-                g_stop = true;
-                memset(pinned, 0, px * sizeof(pixel_t));
-            }
             thread_of[image_num] = thread_id;
-            if (ffs_submit(ctx, slot, image_num) != FFS_OK) {
+            // The compressed chunk is uploaded and decoded on the device (bslz4_gpu.cuh).  The
+            // reference decompresses here on the host (spotfinder.cc:823-841); that path is kept
+            // for chunks the device decoder does not take (FFS_HOST_DECODE=1 forces it).
+            int rc = FFS_ERR_FORMAT;
+            void* pchunk = nullptr;
+            size_t cap = 0;
+            if (!host_decode && ffs_slot_buffers(ctx, slot, nullptr, &pchunk, &cap) == FFS_OK && chunk.size() <= cap) {
+                memcpy(pchunk, chunk.data(), chunk.size());
+                rc = ffs_submit_compressed(ctx, slot, image_num, chunk.size());
+            }
+            if (rc == FFS_ERR_FORMAT) {
+                // decompress straight into the pinned ring slot (no intermediate host copy)
+                if (bslz4::decompress_chunk(chunk.data(), chunk.size(), pinned, px, sizeof(pixel_t), scratch) != 0) {
+                    printf("Error: could not decompress image %zu\n", offset_image_num);
+                    g_stop = true;
+                    memset(pinned, 0, px * sizeof(pixel_t));
+                }
+                rc = ffs_submit(ctx, slot, image_num);
+            }
+            if (rc != FFS_OK) {
                 printf("Error: submit failed: %s\n", ffs_last_error(ctx));
                 g_stop = true;
                 break;
@@ -108,7 +122,10 @@
                 g_stop = true;
                 continue;
             }
-            if (r.status != 0) printf("Warning: image %llu exceeded a spot-list capacity; results truncated\n", (unsigned long long)r.frame_id);
+            if (r.status == FFS_ERR_FORMAT)
+                printf("Error: could not decompress image %llu\n", (unsigned long long)r.frame_id);
+            else if (r.status != 0)
+                printf("Warning: image %llu exceeded a spot-list capacity; results truncated\n", (unsigned long long)r.frame_id);
             if (n > spots.size()) n = spots.size();
             const uint32_t image_num = (uint32_t)r.frame_id;
             // ConnectedComponents::generate_boxes log lines (connected_components.cc:119,133)

@@ -29,6 +29,12 @@ struct StreamSlot {
     int state = 0;               // 0 free, 1 acquired (host filling), 2 in flight
     int stream = 0;
     bool compressed = false;     // submitted through ffs_submit_compressed
+    // The slot's whole per-frame device work, captured once and replayed (all pointers and
+    // launch parameters of a ring slot are fixed): [0] dense-frame path, [1] compressed path.
+    cudaGraphExec_t graph[2] = {nullptr, nullptr};
+    uint32_t graph_kernels[2] = {0, 0};  // kernels inside each graph (launch accounting)
+    uint32_t graph_blocks = 0;           // bitshuffle blocks the compressed graph was built for
+    uint32_t uses[2] = {0, 0};
 };
 
 }  // namespace ffsb
@@ -83,8 +89,9 @@ struct ffs_ctx {
     uint32_t max_blocks = 0;
     uint8_t* h_chunks = nullptr;      // pinned, n_slots * chunk_cap
     uint8_t* d_chunks = nullptr;
-    uint2* h_blocks = nullptr;        // pinned, n_slots * max_blocks {offset, length}
-    uint2* d_blocks = nullptr;
+    size_t blocks_stride = 0;         // bytes per slot: Bslz4Dyn header + max_blocks * uint2 {offset, length}
+    uint8_t* h_blocks = nullptr;      // pinned
+    uint8_t* d_blocks = nullptr;
     unsigned int* d_dec_status = nullptr;  // n_slots
     unsigned int* h_dec_status = nullptr;  // pinned
 

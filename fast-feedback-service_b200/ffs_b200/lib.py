@@ -100,6 +100,7 @@ SYMBOLS = {
     "ffs_pending": (_i, [_vp]),
     "ffs_acquire_compressed": (_i, [_vp, C.POINTER(_i), C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_submit_compressed": (_i, [_vp, _i, C.c_uint64, _sz]),
+    "ffs_slot_buffers": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_decode_chunk_device": (_i, [_vp, _i, _vp, _sz, _vp]),
     "ffs_sweep_begin": (_i, [_vp, C.c_uint64]),
     "ffs_sweep_record_slot": (_i, [_vp, _i, C.c_uint64]),

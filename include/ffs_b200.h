@@ -188,6 +188,11 @@ int ffs_pending(ffs_ctx *ctx);
  * Supported: elem size = bytes_per_pixel, block size <= 8192 bytes (bitshuffle's default). */
 int ffs_acquire_compressed(ffs_ctx *ctx, int *slot, void **pinned_chunk, size_t *capacity);
 int ffs_submit_compressed(ffs_ctx *ctx, int slot, uint64_t frame_id, size_t chunk_bytes);
+/* Both pinned buffers of an acquired slot (any pointer may be NULL): lets a caller fall back
+ * to host decompression + ffs_submit when ffs_submit_compressed returns FFS_ERR_FORMAT
+ * (e.g. a bitshuffle block size above 8192 bytes); the slot stays acquired in that case. */
+int ffs_slot_buffers(ffs_ctx *ctx, int slot, void **pinned_pixels, void **pinned_chunk,
+                     size_t *chunk_capacity);
 /* Parity hook: decode a chunk into device slot `slot` (no further processing) and copy the
  * dense frame back to host memory. */
 int ffs_decode_chunk_device(ffs_ctx *ctx, int slot, const void *chunk, size_t chunk_bytes,

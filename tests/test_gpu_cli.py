@@ -34,10 +34,11 @@ def write_stream(d: Path, frames, mask, bits, omega_increment=None, start=0):
         (d / f"image_{start + i:06d}_2").write_bytes(compress_chunk(f))
 
 
-def run(exe, args, timeout=120):
+def run(exe, args, timeout=120, host_decode=False):
     r, w = os.pipe()
+    env = dict(os.environ, FFS_HOST_DECODE="1" if host_decode else "0")
     proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=subprocess.PIPE,
-                            stderr=subprocess.PIPE)
+                            stderr=subprocess.PIPE, env=env)
     os.close(w)
     lines = []
     with os.fdopen(r) as f:
@@ -47,7 +48,8 @@ def run(exe, args, timeout=120):
     return proc.returncode, lines, out.decode(), err.decode()
 
 
-def test_stills_json_lines_and_stdout(tmp_path):
+@pytest.mark.parametrize("host_decode", [False, True], ids=["device-bslz4", "host-bslz4"])
+def test_stills_json_lines_and_stdout(tmp_path, host_decode):
     g = synth.small_geometry(300, 200)
     mask = synth.make_mask(g)
     frames = synth.make_frames(g, mask, 5, np.uint16, config=8, n_spots=12)
@@ -56,7 +58,8 @@ def test_stills_json_lines_and_stdout(tmp_path):
                                               "--detector", json.dumps({"pixel_size_x": 0.075, "pixel_size_y": 0.075,
                                                                         "beam_center_x": 11.0, "beam_center_y": 7.5,
                                                                         "distance": 150.0, "image_size_x": 300,
-                                                                        "detector": "Eiger"})])
+                                                                        "detector": "Eiger"})],
+                               host_decode=host_decode)
     assert rc == 0 and err == ""
     assert sorted(l["file-number"] for l in lines) == list(range(5))
     found = {int(m.group(1)): int(m.group(2)) for m in re.finditer(r"image\s+(\d+).*?(\d+)\s+strong pixels", out)}
