@@ -51,7 +51,8 @@ static int repack_mask(ffs_ctx* c) {
     {
         const long long groups = (long long)((c->p.width + 7) / 8) * c->p.height;
         group_info_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, c->stream>>>(
-          c->d_valid_bits, c->bits_pitch, (int)c->p.width, (int)c->p.height, c->d_info, c->info_pitch);
+          c->d_valid_bits, c->bits_pitch, (int)c->p.width, (int)c->p.height, c->d_info, c->info_pitch,
+          c->d_mcount, c->m_pitch);
         c->launches++;
     }
     unsigned long long n = 0;
@@ -91,6 +92,9 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     c->info_pitch = round_up(2 * (size_t)((p.width + 7) / 8), 16);
     FFS_CK(c, cudaMalloc(&c->d_info, c->info_pitch * p.height));
     FFS_CK(c, cudaMemset(c->d_info, 0, c->info_pitch * p.height));
+    c->m_pitch = round_up(8 * (size_t)((p.width + 7) / 8), 16);
+    FFS_CK(c, cudaMalloc(&c->d_mcount, c->m_pitch * p.height));
+    FFS_CK(c, cudaMemset(c->d_mcount, 0, c->m_pitch * p.height));
     FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 3));
@@ -141,6 +145,11 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
         cuuint32_t ibox[2] = {(cuuint32_t)FusedGeo<uint16_t>::INFO_ROW_BYTES, (cuuint32_t)FusedGeo<uint16_t>::SR};
         rc = make_tensor_map(c, &c->tm_info, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_info, idims, istrides, ibox);
         if (rc) return rc;
+        cuuint64_t mdims[2] = {(cuuint64_t)(c->m_pitch / 2), p.height};
+        cuuint64_t mstrides[1] = {c->m_pitch};
+        cuuint32_t mbox[2] = {(cuuint32_t)(ExtGeo<uint16_t>::M_ROW_BYTES / 2), 4};
+        rc = make_tensor_map(c, &c->tm_m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, c->d_mcount, mdims, mstrides, mbox);
+        if (rc) return rc;
         c->have_tm = true;
     }
     rc = extended_setup(c);
@@ -184,6 +193,7 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_mask);
     cudaFree(c->d_valid_bits);
     cudaFree(c->d_info);
+    cudaFree(c->d_mcount);
     cudaFree(c->d_frames);
     cudaFree(c->d_strong);
     cudaFree(c->d_ext1);

@@ -11,8 +11,36 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     fill_thresh_args(c, a, first_slot, n);
     a.strong_bits = reinterpret_cast<uint32_t*>(c->d_ext1);
     a.strong_count = c->d_ext_count;
-    a.force_brute = 1;
-    resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
+    static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
+    if (brute) {
+        a.force_brute = 1;
+        resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
+    } else {
+        // streaming first pass (extended_stream.cuh)
+        using G = FusedGeo<PixelT>;
+        using E = ExtGeo<PixelT>;
+        constexpr int kStages = 2, kWarps = 3;
+        auto kern = ext_pass1_kernel<PixelT, kStages, kWarps>;
+        const int smem = kWarps * E::smem_per_warp(kStages) + 128;
+        static bool attr_done[64] = {};
+        if (!attr_done[c->p.device & 63]) {
+            FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            attr_done[c->p.device & 63] = true;
+        }
+        a.force_brute = 0;
+        a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
+        const int resident = std::max(1, (int)(200 * 1024 / E::smem_per_warp(kStages)));
+        const long long want = 2LL * c->sm_count * resident;
+        int best = 4 * 8 - 6;
+        for (int groups = 64; groups >= 8; groups -= 2) {
+            best = groups * 4 - 6;
+            if ((long long)n * a.n_strips * ((a.height + best - 1) / best) >= want) break;
+        }
+        a.tile_rows = best;
+        a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
+        const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
+        kern<<<(unsigned)((tasks + kWarps - 1) / kWarps), kWarps * 32, smem, st>>>(c->tm_img8, c->tm_info, c->tm_m, a);
+    }
     // erosion -> B plane (validity of the second pass) + list of core pixels
     ErodeArgs e{};
     e.width = (int)c->p.width;

@@ -57,6 +57,8 @@ struct ffs_ctx {
     uint8_t* d_valid_bits = nullptr;  // 1-bit validity plane
     uint8_t* d_info = nullptr;        // per group of 8 pixels: {validity byte, m_ub} (dispersion_fused.cuh)
     size_t info_pitch = 0;            // bytes per row of d_info (multiple of 16)
+    uint8_t* d_mcount = nullptr;      // per pixel: valid pixels in its clipped 7x7 window (extended_stream.cuh)
+    size_t m_pitch = 0;
     uint8_t* d_frames = nullptr;      // n_slots pitched frames
     uint8_t* d_strong = nullptr;      // n_slots strong bit-planes
     uint8_t* d_ext1 = nullptr;        // extended: first-pass dispersion bit-planes
@@ -99,6 +101,7 @@ struct ffs_ctx {
     CUtensorMap tm_img{};     // 3D: x, y, slot
     CUtensorMap tm_valid{};   // 2D validity bytes
     CUtensorMap tm_info{};    // 2D group info bytes
+    CUtensorMap tm_m{};       // 2D per-pixel window counts, as u16 pairs
     CUtensorMap tm_img8{};    // 3D image, 256-pixel box (fused kernel; == tm_img for 16-bit pixels)
     CUtensorMap tm_valid2{};  // 3D eroded validity (extended second pass): x, y, slot
     bool have_tm = false;

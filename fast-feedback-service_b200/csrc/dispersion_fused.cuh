@@ -71,7 +71,8 @@ struct FusedGeo {
 // m_ub = max over the group's mask-valid pixels of the number of valid pixels in the
 // image-clipped 7x7 window (standalone.cc:126-130 clipping).
 __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t bits_pitch, int width,
-                                  int height, uint8_t* __restrict__ info, size_t info_pitch) {
+                                  int height, uint8_t* __restrict__ info, size_t info_pitch,
+                                  uint8_t* __restrict__ mplane, size_t m_pitch) {
     const int groups = (width + 7) / 8;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (long long)groups * height) return;
@@ -97,6 +98,18 @@ __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t
     uint8_t* out = info + (size_t)row * info_pitch + 2 * gi;
     out[0] = (uint8_t)vb;
     out[1] = (uint8_t)mub;
+    // per-pixel window counts (extended_stream.cuh): 8 bytes per group, 0 beyond the width
+    uint2 mm;
+    mm.x = m[0] | (m[1] << 8) | (m[2] << 16) | (m[3] << 24);
+    mm.y = m[4] | (m[5] << 8) | (m[6] << 16) | (m[7] << 24);
+    const int left = width - 8 * gi;  // pixels of this group inside the image
+    if (left < 8) {
+        const unsigned long long keep = (1ull << (8 * left)) - 1ull;
+        const unsigned long long v = ((unsigned long long)mm.y << 32 | mm.x) & keep;
+        mm.x = (uint32_t)v;
+        mm.y = (uint32_t)(v >> 32);
+    }
+    *reinterpret_cast<uint2*>(mplane + (size_t)row * m_pitch + 8 * gi) = mm;
 }
 
 // ---- row front end: masked + clamped packed words, max of the masked raw values -----------

@@ -1,0 +1,335 @@
+// extended_stream.cuh -- first pass of DispersionExtendedThreshold as an HBM-streaming kernel.
+//
+//   compute_dispersion_threshold (baseline/spotfinder/baseline.cpp:415-475):
+//       D[k] = mask[k] && m >= min_count && x >= 0 && a > c
+//       a = m*y - x*x - x*(m-1),  c = x * nsig_b * sqrt(2*(m-1))       (7x7 window sums m, x, y)
+//
+// Unlike the standard algorithm there is no sparse signal test to prune with: every pixel
+// needs its own window sums.  The kernel shares the fused dispersion kernel's skeleton (one
+// warp per 240-column strip, TMA-fed 4-row stages, 8-row shared ring, no block barriers) and
+// forms EXACT separable box sums for all pixels whose window holds no pixel above 1169:
+//   x : values packed two per word, vertical running sum in packed form, horizontal 7-tap
+//       sums from warp shuffles (as in dispersion_fused.cuh);
+//   y : squares (<= 1169^2, so a 49-pixel sum stays below 2^26) as 32-bit running column sums
+//       -- the outgoing row's squares are recomputed from the ring's packed values -- and
+//       7-tap sums from 6 shuffles;
+//   m : the number of mask-valid pixels in the clipped window is a property of the mask,
+//       precomputed per pixel (group_info_kernel) and TMA-loaded as a third tile.
+// The comparison  m*y - x^2 > x * K(m),  K(m) = m-1 + nsig_b*sqrt(2(m-1)),  is made in fp32 with
+// an explicit error bound; only pixels inside that bound, and windows that contain a pixel
+// above 1169 (or, for 32-bit data, an uncounted pixel >= 2^24), are queued and decided by the
+// exact integer/fp64 evaluation (resolve_pixel<.., EXT_PASS1 = true>).  The D plane is written
+// as one byte per pixel group; queued pixels are OR-ed in afterwards.
+#pragma once
+#include "dispersion_fused.cuh"
+
+namespace ffsb {
+
+template <typename PixelT>
+struct ExtGeo {
+    using F = FusedGeo<PixelT>;
+    static constexpr int SR = 4;
+    static constexpr unsigned CLAMP = 1169u;     // 49 * 1169^2 < 2^26
+    static constexpr int M_ROW_BYTES = 272;      // 256 per-pixel counts + 16 B of alignment lead-in
+    static constexpr int M_STAGE_BYTES = (SR * M_ROW_BYTES + 127) / 128 * 128;
+    static constexpr int STAGE_BYTES = F::IMG_STAGE_BYTES + F::INFO_STAGE_BYTES + M_STAGE_BYTES;
+    static constexpr int TX_BYTES = F::IMG_STAGE_BYTES + SR * F::INFO_ROW_BYTES + SR * M_ROW_BYTES;
+    static constexpr int GQ_CAP = 64, PQ_CAP = 288;
+    static constexpr int QUEUE_BYTES = (GQ_CAP + PQ_CAP) * 4;
+    static_assert(QUEUE_BYTES % 128 == 0, "alignment");
+    __host__ __device__ static constexpr int smem_per_warp(int stages) {
+        return stages * STAGE_BYTES + F::RING_BYTES + QUEUE_BYTES + 128;
+    }
+};
+
+// Exact decision for queued pixels (out of line: rare path).  state = qn | pqn << 8.
+template <typename PixelT>
+__device__ __noinline__ uint32_t ext_resolve(const ThreshArgs* __restrict__ ap, uint32_t* gq, int x0, int r0,
+                                             int z, uint32_t state, int n, bool flush_all) {
+    using E = ExtGeo<PixelT>;
+    const ThreshArgs& a = *ap;
+    const int lane = threadIdx.x & 31;
+    uint32_t* pq = gq + E::GQ_CAP;
+    const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
+    int qn = state & 0xff, pqn = state >> 8;
+    unsigned found = 0;
+    auto resolve_entry = [&](uint32_t e) {
+        const int col = e & 0x1fff, row = e >> 13;
+        if (resolve_pixel<PixelT, 3, true>(a, frame, a.valid_bits, col, row)) {
+            set_strong(a, z, col, row);
+            ++found;
+        }
+    };
+    if (n > 0) {
+        uint32_t bits = 0;
+        int col0 = 0, row = 0;
+        if (lane < n) {
+            const uint32_t e = gq[qn - n + lane];
+            bits = e >> 14;
+            col0 = x0 + (int)(e & 31u) * 8;
+            row = r0 + (int)((e >> 5) & 0x1ffu);
+        }
+        qn -= n;
+        int cnt = __popc(bits), incl = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        int pos = pqn + incl - cnt;
+        while (bits) {
+            const int j = __ffs(bits) - 1;
+            bits &= bits - 1;
+            pq[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
+        }
+        pqn += __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+        while (pqn >= 32) {
+            pqn -= 32;
+            resolve_entry(pq[pqn + lane]);
+        }
+        __syncwarp();
+    }
+    if (flush_all && pqn > 0) {
+        if (lane < pqn) resolve_entry(pq[lane]);
+        pqn = 0;
+    }
+    for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
+    if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
+    return (uint32_t)qn | ((uint32_t)pqn << 8);
+}
+
+template <typename PixelT, int STAGES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+  ext_pass1_kernel(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_info,
+                   const __grid_constant__ CUtensorMap tm_m, const __grid_constant__ ThreshArgs a) {
+    using G = FusedGeo<PixelT>;
+    using E = ExtGeo<PixelT>;
+    constexpr int SR = 4, KH = 3, PPL = 8;
+    constexpr uint32_t CL = E::CLAMP;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ float2 ktab[64];  // {m, K(m) = m-1 + nsig_b*sqrt(2(m-1))}
+    for (int t = threadIdx.x; t < 64; t += WARPS * 32) {
+        const float m1 = (float)max(t - 1, 0);
+        ktab[t] = make_float2((float)t, m1 + (float)a.nsig_b * sqrtf(2.0f * m1));
+    }
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const long long task = (long long)blockIdx.x * WARPS + warp;
+    const long long n_tasks = (long long)a.n_frames * a.n_row_tiles * a.n_strips;
+    if (task >= n_tasks) return;
+    const int strip = (int)(task % a.n_strips);
+    const int rt = (int)((task / a.n_strips) % a.n_row_tiles);
+    const int z = a.slot0 + (int)(task / ((long long)a.n_strips * a.n_row_tiles));
+
+    uint8_t* smem_al = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
+    uint8_t* wsm = smem_al + (size_t)warp * E::smem_per_warp(STAGES);
+    uint8_t* stage_base = wsm;
+    uint8_t* ring = wsm + STAGES * E::STAGE_BYTES;
+    uint32_t* gq = reinterpret_cast<uint32_t*>(ring + G::RING_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + G::RING_BYTES + E::QUEUE_BYTES);
+
+    const int r0 = rt * a.tile_rows;
+    const int row_end = min(r0 + a.tile_rows, a.height);
+    const int n_load_rows = (row_end - r0) + 2 * KH;
+    const int n_groups = (n_load_rows + SR - 1) / SR;
+    const int x0 = strip * G::OUT_COLS - PPL;
+    const int y_first = r0 - KH;
+    const int info_b = 2 * (strip * G::OUT_LANES - 1);
+    const int info_b0 = info_b & ~15;
+    const int m_x = (x0 - 8) / 2;  // u16 units; x0 - 8 is a multiple of 16 (and may be negative)
+
+    if (lane == 0) {
+        for (int s = 0; s < STAGES; ++s) ptx::mbar_init(bars + s, 1);
+        ptx::fence_mbar_init();
+    }
+    {
+        const uint4 zero = make_uint4(0, 0, 0, 0);
+        for (int k = lane; k < G::RING_BYTES / 16; k += 32) reinterpret_cast<uint4*>(ring)[k] = zero;
+    }
+    __syncwarp();
+
+    auto issue = [&](int g, int s) {
+        uint8_t* dst = stage_base + s * E::STAGE_BYTES;
+        ptx::mbar_arrive_expect_tx(bars + s, E::TX_BYTES);
+        ptx::tma_load_3d(dst, &tm_img, bars + s, x0, y_first + g * SR, z);
+        ptx::tma_load_2d(dst + G::IMG_STAGE_BYTES, &tm_info, bars + s, info_b0, y_first + g * SR);
+        // the count tile is row-shifted: load-row i carries the counts of its centre row i-3
+        ptx::tma_load_2d(dst + G::IMG_STAGE_BYTES + G::INFO_STAGE_BYTES, &tm_m, bars + s, m_x,
+                         y_first + g * SR - KH);
+    };
+    if (lane == 0) {
+        for (int g = 0; g < STAGES && g < n_groups; ++g) issue(g, g);
+    }
+
+    const bool out_lane = lane >= 1 && lane <= G::OUT_LANES;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int group = strip * G::OUT_LANES + lane - 1;            // pixel group of this lane
+    const bool store_lane = out_lane && group < (int)a.strong_pitch;
+    uint8_t* dplane = reinterpret_cast<uint8_t*>(a.strong_bits) + (size_t)z * a.strong_frame_stride;
+    int qn = 0, pqn = 0;
+
+    uint32_t V[4] = {0, 0, 0, 0};                  // packed column sums of x over the last 7 rows
+    uint32_t Vy[8] = {0, 0, 0, 0, 0, 0, 0, 0};     // column sums of the squares
+    uint32_t big7 = 0;                             // bit r: row i-r of this lane holds a pixel > CLAMP
+    uint32_t hi1 = 0, hi2 = 0, hi3 = 0;            // validity bytes of rows i-1, i-2, i-3
+    uint8_t* ring_lane = ring + lane * 16;
+    const int pimg_off = lane * PPL * (int)sizeof(PixelT);
+    const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 2 * lane;
+    const int pm_off = G::IMG_STAGE_BYTES + G::INFO_STAGE_BYTES + 8 + 8 * lane;
+
+    int s = 0;
+    uint32_t phase = 0;
+    for (int g = 0; g < n_groups; ++g) {
+        ptx::mbar_wait(bars + s, phase);
+        const uint8_t* st = stage_base + s * E::STAGE_BYTES;
+        uint8_t* rcur = ring_lane + ((g & 1) ? SR * G::RING_ROW_BYTES : 0);
+        uint8_t* roth = ring_lane + ((g & 1) ? 0 : SR * G::RING_ROW_BYTES);
+#pragma unroll
+        for (int u = 0; u < SR; ++u) {
+            const int i = g * SR + u;
+            // ---- load, mask, clamp ------------------------------------------------------------
+            const uint32_t info = *reinterpret_cast<const uint16_t*>(st + pinfo_off + u * G::INFO_ROW_BYTES);
+            uint32_t c[4];
+            bool big;
+            if constexpr (sizeof(PixelT) == 2) {
+                const uint4 raw = ptx::lds128(st + u * G::IMG_ROW_BYTES + pimg_off);
+                const uint32_t zlo = (info & 0xfu) * 0x10204080u;
+                const uint32_t zhi = ((info >> 4) & 0xfu) * 0x10204080u;
+                const uint32_t w0 = raw.x & ptx::prmt(zlo, 0u, 0x9988u);
+                const uint32_t w1 = raw.y & ptx::prmt(zlo, 0u, 0xbbaau);
+                const uint32_t w2 = raw.z & ptx::prmt(zhi, 0u, 0x9988u);
+                const uint32_t w3 = raw.w & ptx::prmt(zhi, 0u, 0xbbaau);
+                constexpr uint32_t CL2 = CL | (CL << 16);
+                c[0] = __vminu2(w0, CL2);
+                c[1] = __vminu2(w1, CL2);
+                c[2] = __vminu2(w2, CL2);
+                c[3] = __vminu2(w3, CL2);
+                big = ((w0 ^ c[0]) | (w1 ^ c[1]) | (w2 ^ c[2]) | (w3 ^ c[3])) != 0;
+            } else {
+                const uint4 ra = ptx::lds128(st + u * G::IMG_ROW_BYTES + pimg_off);
+                const uint4 rb = ptx::lds128(st + u * G::IMG_ROW_BYTES + pimg_off + 16);
+                const uint32_t r[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+                uint32_t cl[8], vmax = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t v = (info & (1u << j)) ? r[j] : 0u;
+                    vmax = max(vmax, v);
+                    cl[j] = min(v, CL);
+                }
+                big = vmax > CL;  // includes uncounted pixels >= 2^24
+#pragma unroll
+                for (int k = 0; k < 4; ++k) c[k] = cl[2 * k] | (cl[2 * k + 1] << 16);
+            }
+            // ---- vertical running sums; the outgoing row's squares come from the ring ------------
+            uint8_t* oldp = (u + 1 < SR) ? rcur + (u + 1) * G::RING_ROW_BYTES : roth;
+            const uint4 old = ptx::lds128(oldp);
+            const uint32_t o[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                V[k] = V[k] + c[k] - o[k];
+                const uint32_t nl = c[k] & 0xffffu, nh = c[k] >> 16, ol = o[k] & 0xffffu, oh = o[k] >> 16;
+                Vy[2 * k] = Vy[2 * k] + nl * nl - ol * ol;
+                Vy[2 * k + 1] = Vy[2 * k + 1] + nh * nh - oh * oh;
+            }
+            *reinterpret_cast<uint4*>(rcur + u * G::RING_ROW_BYTES) = make_uint4(c[0], c[1], c[2], c[3]);
+            big7 = ((big7 << 1) | (big ? 1u : 0u)) & 0x7fu;
+
+            const int out_row = r0 + i - 2 * KH;
+            if (i >= 2 * KH && out_row < row_end) {  // warp-uniform
+                // windows that hold a clamped pixel: this lane's or a neighbour's last 7 rows
+                const unsigned bm = __ballot_sync(0xffffffffu, big7 != 0);
+                const bool flagged = ((bm >> (lane > 0 ? lane - 1 : 0)) & (lane > 0 ? 7u : 3u)) != 0;
+                // ---- horizontal sums ------------------------------------------------------------
+                const uint32_t l2 = __shfl_up_sync(0xffffffffu, V[2], 1);
+                const uint32_t l3 = __shfl_up_sync(0xffffffffu, V[3], 1);
+                const uint32_t rr0 = __shfl_down_sync(0xffffffffu, V[0], 1);
+                const uint32_t rr1 = __shfl_down_sync(0xffffffffu, V[1], 1);
+                uint32_t Ex[14], Ey[14];
+                Ex[0] = l2 >> 16;
+                Ex[1] = l3 & 0xffffu;
+                Ex[2] = l3 >> 16;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    Ex[3 + 2 * k] = V[k] & 0xffffu;
+                    Ex[4 + 2 * k] = V[k] >> 16;
+                }
+                Ex[11] = rr0 & 0xffffu;
+                Ex[12] = rr0 >> 16;
+                Ex[13] = rr1 & 0xffffu;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    Ey[k] = __shfl_up_sync(0xffffffffu, Vy[5 + k], 1);
+                    Ey[11 + k] = __shfl_down_sync(0xffffffffu, Vy[k], 1);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) Ey[3 + k] = Vy[k];
+                uint32_t Hx[8], Hy[8];
+                Hx[0] = Ex[0] + Ex[1] + Ex[2] + Ex[3] + Ex[4] + Ex[5] + Ex[6];
+                Hy[0] = Ey[0] + Ey[1] + Ey[2] + Ey[3] + Ey[4] + Ey[5] + Ey[6];
+#pragma unroll
+                for (int j = 1; j < 8; ++j) {
+                    Hx[j] = Hx[j - 1] + Ex[j + 6] - Ex[j - 1];
+                    Hy[j] = Hy[j - 1] + Ey[j + 6] - Ey[j - 1];
+                }
+                // ---- per-pixel test in fp32 with an error bound --------------------------------------
+                const uint2 mw = *reinterpret_cast<const uint2*>(st + pm_off + u * E::M_ROW_BYTES);
+                const uint32_t vb = hi3 & 0xffu;  // validity of the centre row's pixels
+                uint32_t dbits = 0, border = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t m = ((j < 4 ? mw.x : mw.y) >> (8 * (j & 3))) & 0xffu;
+                    const float2 mk = ktab[m];
+                    const float xf = (float)Hx[j], yf = (float)Hy[j];
+                    const float t = mk.x * yf, uu = xf * xf, rhs = xf * mk.y;
+                    const float lhs = t - uu;
+                    const float sl = 4e-7f * (t + uu + rhs);
+                    const bool ok = ((vb >> j) & 1u) && (int)m >= a.min_count;
+                    const bool hi = (lhs - sl) > rhs, lo = (lhs + sl) > rhs;
+                    dbits |= (ok && hi) ? (1u << j) : 0u;
+                    border |= (ok && lo && !hi) ? (1u << j) : 0u;
+                }
+                if (flagged) {  // sums are not exact here: decide every valid pixel exactly
+                    dbits = 0;
+                    border = vb;
+                }
+                if (store_lane) dplane[(size_t)out_row * a.strong_pitch + group] = (uint8_t)dbits;
+                const unsigned cnt = __popc(out_lane ? dbits : 0u);
+                if (cnt) atomicAdd(a.strong_count + z, cnt);
+                const bool push = out_lane && border != 0;
+                const unsigned ball = __ballot_sync(0xffffffffu, push);
+                if (ball) {
+                    if (push)
+                        gq[qn + __popc(ball & lt_mask)] =
+                          (uint32_t)lane | ((uint32_t)(out_row - r0) << 5) | (border << 14);
+                    qn += __popc(ball);
+                    __syncwarp();
+                    if (qn >= 32) {
+                        const uint32_t st2 = ext_resolve<PixelT>(&a, gq, x0, r0, z,
+                                                                 (uint32_t)qn | ((uint32_t)pqn << 8), 32, false);
+                        qn = st2 & 0xff;
+                        pqn = st2 >> 8;
+                    }
+                }
+            }
+            hi3 = hi2; hi2 = hi1; hi1 = info;
+        }
+        __syncwarp();
+        if (lane == 0 && g + STAGES < n_groups) {
+            ptx::fence_proxy_async();
+            issue(g + STAGES, s);
+        }
+        if (++s == STAGES) {
+            s = 0;
+            phase ^= 1u;
+        }
+    }
+    __syncwarp();
+    if (qn > 0 || pqn > 0)
+        ext_resolve<PixelT>(&a, gq, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
+}
+
+}  // namespace ffsb

@@ -4,6 +4,7 @@
 #include "mask.cuh"
 #include "threshold.cuh"
 #include "dispersion_fused.cuh"
+#include "extended_stream.cuh"
 #include "extended.cuh"
 #include "cc.cuh"
 #include "cc3d.cuh"
