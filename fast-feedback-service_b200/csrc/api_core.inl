@@ -318,6 +318,8 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
     a.sig_k = (float)(c->p.nsig_s * (1.0 - 1e-4));
     a.thr_floor = (int)std::min(std::floor(c->p.threshold), 1073741824.0);
+    a.mcount = c->d_mcount;
+    a.m_pitch = c->m_pitch;
 }
 
 template <typename PixelT, int PPL>

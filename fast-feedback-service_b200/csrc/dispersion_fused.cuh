@@ -34,6 +34,9 @@
 
 namespace ffsb {
 
+#ifndef FUSED_DP2A
+#define FUSED_DP2A 1
+#endif
 #ifndef FUSED_MIN_WARPS_PER_SM
 #define FUSED_MIN_WARPS_PER_SM 12  // register cap = 65536 / (32 * this)
 #endif
@@ -56,10 +59,11 @@ struct FusedGeo {
     static constexpr int RING_ROWS = 2 * SR;
     static constexpr int RING_ROW_BYTES = 32 * 16;
     static constexpr int RING_BYTES = RING_ROWS * RING_ROW_BYTES;
-    static constexpr int GQ_CAP = 64;        // pending candidate groups (< 32 + 30)
+    static constexpr int GQ_CAP = 96;        // pending candidate groups (< 32 + 2 rows * 30)
     static constexpr int PQ_CAP = 288;       // pending candidate pixels (< 32 + 32 * 8)
     // per queued group: 4 B meta + 32 B window sums + 16 B clamped centre-row words
-    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + PQ_CAP * 4;
+    // plus two pixel queues: windows that are fully valid (fast exact test) / all others
+    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + 2 * PQ_CAP * 4;
     static_assert(RING_ROWS > 2 * KH, "ring must hold the 7-row window");
     static_assert(IMG_STAGE_BYTES % 128 == 0 && QUEUE_BYTES % 128 == 0, "TMA destination alignment");
     __host__ __device__ static constexpr int smem_per_warp(int stages) {
@@ -155,7 +159,7 @@ __device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_
 // ---- rare path, deliberately NOT inlined (one copy of ~2000 instructions instead of five) ----
 // Expands the last `n` queued groups to candidate pixels with each pixel's own window sum,
 // then resolves the queued pixels 32 at a time (all of them if flush_all) with the exact
-// test.  state = qn | pqn << 8 (both warp-uniform); the new state is returned.
+// test.  state = qn | pqn << 8 | pgn << 20 (all warp-uniform); the new state is returned.
 template <typename PixelT>
 __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap, uint8_t* qbase,
                                                const float* rcp_tab, int x0, int r0, int z, uint32_t state,
@@ -167,14 +171,23 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
     uint32_t* gq = reinterpret_cast<uint32_t*>(qbase);
     uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);
     uint4* cq = hq + 2 * G::GQ_CAP;
-    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);
+    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);  // pixels with a full 7x7 window
+    uint32_t* pg = pq + G::PQ_CAP;                               // pixels near the mask / the edge
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
     const uint8_t* valid = a.valid_bits;
     const float sk = a.sig_k;
     const int thr_floor = a.thr_floor;
-    int qn = state & 0xff, pqn = state >> 8;
+    int qn = state & 0xff, pqn = (state >> 8) & 0xfff, pgn = state >> 20;
     unsigned found = 0;
-    auto resolve_entry = [&](uint32_t e) {
+    auto resolve_full = [&](uint32_t e) {
+        const int col = e & 0x1fff, row = e >> 13;
+        if (a.force_brute == 2) return;
+        if (resolve_pixel_full<PixelT, KH>(a, frame, col, row)) {
+            set_strong(a, z, col, row);
+            ++found;
+        }
+    };
+    auto resolve_any = [&](uint32_t e) {
         const int col = e & 0x1fff, row = e >> 13;
         if (a.force_brute == 2) return;
         if (resolve_pixel_wide<PixelT, KH>(a, frame, valid, col, row)) {
@@ -183,7 +196,7 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         }
     };
     if (n > 0) {
-        uint32_t bits = 0;
+        uint32_t bits = 0, full = 0;
         int col0 = 0, row = 0;
         if (lane < n) {
             const int qi = qn - n + lane;
@@ -193,6 +206,7 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
             const float rc = rcp_tab[e >> 14];
             col0 = x0 + (int)(e & 31u) * PPL;
             row = r0 + (int)((e >> 5) & 0x1ffu);
+            const uint2 mc = *reinterpret_cast<const uint2*>(a.mcount + (size_t)row * a.m_pitch + col0);
             uint32_t v[8], vb = 0xffu;
             if constexpr (sizeof(PixelT) == 2) {
                 // masked + clamped centre-row values queued by the streaming loop: a masked pixel
@@ -217,36 +231,55 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
                 uint32_t T = (uint32_t)max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
                 if constexpr (sizeof(PixelT) == 2) T = min(T, G::CLAMP - 1u);
                 bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
+                const uint32_t mj = ((j < 4 ? mc.x : mc.y) >> (8 * (j & 3))) & 0xffu;
+                full |= mj == 49u ? (1u << j) : 0u;
             }
         }
         qn -= n;
-        int cnt = __popc(bits), incl = cnt;
+        const uint32_t bf = bits & full, bg = bits & ~full;
+        // one scan for both queues: fast count in the low half, general count in the high half
+        const uint32_t cnt = (uint32_t)__popc(bf) | ((uint32_t)__popc(bg) << 16);
+        uint32_t incl = cnt;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, off);
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
             if (lane >= off) incl += t;
         }
-        int pos = pqn + incl - cnt;
-        while (bits) {
-            const int j = __ffs(bits) - 1;
-            bits &= bits - 1;
+        const uint32_t excl = incl - cnt;
+        int pos = pqn + (int)(excl & 0xffffu);
+        for (uint32_t b = bf; b;) {
+            const int j = __ffs(b) - 1;
+            b &= b - 1;
             pq[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
         }
-        pqn += __shfl_sync(0xffffffffu, incl, 31);
+        pos = pgn + (int)(excl >> 16);
+        for (uint32_t b = bg; b;) {
+            const int j = __ffs(b) - 1;
+            b &= b - 1;
+            pg[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        pqn += (int)(tot & 0xffffu);
+        pgn += (int)(tot >> 16);
         __syncwarp();
         while (pqn >= 32) {
             pqn -= 32;
-            resolve_entry(pq[pqn + lane]);
+            resolve_full(pq[pqn + lane]);
+        }
+        while (pgn >= 32) {
+            pgn -= 32;
+            resolve_any(pg[pgn + lane]);
         }
         __syncwarp();
     }
-    if (flush_all && pqn > 0) {
-        if (lane < pqn) resolve_entry(pq[lane]);
-        pqn = 0;
+    if (flush_all) {
+        if (lane < pqn) resolve_full(pq[lane]);
+        if (lane < pgn) resolve_any(pg[lane]);
+        pqn = pgn = 0;
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
     if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
-    return (uint32_t)qn | ((uint32_t)pqn << 8);
+    return (uint32_t)qn | ((uint32_t)pqn << 8) | ((uint32_t)pgn << 20);
 }
 
 template <typename PixelT, int STAGES, int WARPS>
@@ -314,7 +347,8 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float sk = a.sig_k;             // nsig_s * (1 - 1e-4)
     const int thr_floor = a.thr_floor;
-    int qn = 0, pqn = 0;     // warp-uniform queue fill levels
+    int qn = 0;              // warp-uniform fill level of the group queue
+    uint32_t pstate = 0;     // fill levels of the two pixel queues (<< 8, << 20)
     uint8_t* qbase = reinterpret_cast<uint8_t*>(gq);
 
     uint32_t V[4] = {0, 0, 0, 0};   // packed column sums of the last 7 rows
@@ -358,7 +392,7 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
         }
         // ---- phase B: horizontal sums, group threshold, pass flag (no branches) --------------
         uint32_t Hx[SR][8];
-        bool pass[SR];
+        unsigned ball[SR];
 #pragma unroll
         for (int u = 0; u < SR; ++u) {
             const int i = g * SR + u;  // load-row index within the task
@@ -367,6 +401,31 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             const uint32_t l3 = __shfl_up_sync(0xffffffffu, Vs[u][3], 1);
             const uint32_t rr0 = __shfl_down_sync(0xffffffffu, Vs[u][0], 1);
             const uint32_t rr1 = __shfl_down_sync(0xffffffffu, Vs[u][1], 1);
+#if FUSED_DP2A
+            // 7-tap sums of 16-bit halves with IDP.2A (d = c + a.lo * b0 + a.hi * b1): the
+            // integer dot product issues on the FMA pipe, which this loop otherwise leaves idle,
+            // while every unpack / add it replaces would queue on the ALU pipe.
+            // Words: W0 = l2, W1 = l3, W2..W5 = own V[0..3], W6 = rr0, W7 = rr1; window j = halves j .. j+6
+            // of the 16-half sequence, starting at W0.hi.
+            constexpr uint32_t LO = 0x0001u, HI = 0x0100u, BOTH = 0x0101u;
+            const uint32_t* Wv = Vs[u];
+            const uint32_t a23 = __dp2a_lo(Wv[0], BOTH, __dp2a_lo(Wv[1], BOTH, 0u));
+            const uint32_t a45 = __dp2a_lo(Wv[2], BOTH, __dp2a_lo(Wv[3], BOTH, 0u));
+            const uint32_t t1 = __dp2a_lo(l3, BOTH, a23);      // W1 + W2 + W3
+            const uint32_t t2 = __dp2a_lo(Wv[2], BOTH, a23);   // W2 + W3 + W4
+            const uint32_t t3 = __dp2a_lo(Wv[1], BOTH, a45);   // W3 + W4 + W5
+            const uint32_t t4 = __dp2a_lo(rr0, BOTH, a45);     // W4 + W5 + W6
+            Hx[u][0] = __dp2a_lo(l2, HI, t1);
+            Hx[u][1] = __dp2a_lo(Wv[2], LO, t1);
+            Hx[u][2] = __dp2a_lo(l3, HI, t2);
+            Hx[u][3] = __dp2a_lo(Wv[3], LO, t2);
+            Hx[u][4] = __dp2a_lo(Wv[0], HI, t3);
+            Hx[u][5] = __dp2a_lo(rr0, LO, t3);
+            Hx[u][6] = __dp2a_lo(Wv[1], HI, t4);
+            Hx[u][7] = __dp2a_lo(rr1, LO, t4);
+            const uint32_t xmin = min(min(min(Hx[u][0], Hx[u][1]), min(Hx[u][2], Hx[u][3])),
+                                      min(min(Hx[u][4], Hx[u][5]), min(Hx[u][6], Hx[u][7])));
+#else
             uint32_t E[14];
             E[0] = l2 >> 16;
             E[1] = l3 & 0xffffu;
@@ -386,34 +445,37 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
                 Hx[u][j] = Hx[u][j - 1] + E[j + 6] - E[j - 1];
                 xmin = min(xmin, Hx[u][j]);
             }
+#endif
             // group threshold on the raw value: T = floor(mu + nsig_s' sqrt(mu)), mu = x_lb / m_ub
             const float mu = (float)xmin * rcp_tab[mub[u]];
             float sq;
             asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
             const int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
-            pass[u] = out_lane && vmc[u] > (uint32_t)T && i >= 2 * KH && out_row < row_end;
+            ball[u] = __ballot_sync(0xffffffffu,
+                                    out_lane && vmc[u] > (uint32_t)T && i >= 2 * KH && out_row < row_end);
         }
-        // ---- phase C: queue the passing groups; resolve when 32 are pending -------------------
+        // ---- phase C: queue the passing groups (predicated stores, no divergence); resolve
+        // when 32 are pending -- checked every two rows, which GQ_CAP allows for ----------------
+        const uint32_t gq_s = ptx::smem_u32(gq), hq_s = ptx::smem_u32(hq), cq_s = ptx::smem_u32(cq);
 #pragma unroll
         for (int u = 0; u < SR; ++u) {
-            const unsigned ball = __ballot_sync(0xffffffffu, pass[u]);
-            if (ball) {
-                if (pass[u]) {
-                    const int qi = qn + __popc(ball & lt_mask);
-                    gq[qi] = (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[u] << 14);
-                    hq[2 * qi] = make_uint4(Hx[u][0], Hx[u][1], Hx[u][2], Hx[u][3]);
-                    hq[2 * qi + 1] = make_uint4(Hx[u][4], Hx[u][5], Hx[u][6], Hx[u][7]);
-                    // ring slot of the centre row i-3 is (i + 5) & 7
-                    cq[qi] = ptx::lds128((u < SR - 1) ? roth + (u + 1) * G::RING_ROW_BYTES : rcur);
-                }
-                qn += __popc(ball);
+            const bool p = (ball[u] >> lane) & 1u;
+            const int qi = qn + __popc(ball[u] & lt_mask);
+            // ring slot of the centre row i-3 is (i + 5) & 7
+            const uint4 cw = ptx::lds128((u < SR - 1) ? roth + (u + 1) * G::RING_ROW_BYTES : rcur);
+            ptx::sts32_if(p, gq_s + 4 * qi, (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[u] << 14));
+            ptx::sts128_if(p, hq_s + 32 * qi, Hx[u][0], Hx[u][1], Hx[u][2], Hx[u][3]);
+            ptx::sts128_if(p, hq_s + 32 * qi + 16, Hx[u][4], Hx[u][5], Hx[u][6], Hx[u][7]);
+            ptx::sts128_if(p, cq_s + 16 * qi, cw.x, cw.y, cw.z, cw.w);
+            qn += __popc(ball[u]);
+            if ((u & 1) && qn >= 32) {
                 __syncwarp();
-                if (qn >= 32) {
+                do {
                     const uint32_t st2 = fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z,
-                                                               (uint32_t)qn | ((uint32_t)pqn << 8), 32, false);
+                                                               (uint32_t)qn | pstate, 32, false);
                     qn = st2 & 0xff;
-                    pqn = st2 >> 8;
-                }
+                    pstate = st2 & ~0xffu;
+                } while (qn >= 32);
             }
         }
         }
@@ -429,8 +491,8 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
         }
     }
     __syncwarp();
-    if (qn > 0 || pqn > 0)
-        fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
+    if (qn > 0 || pstate)
+        fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z, (uint32_t)qn | pstate, qn, true);
 }
 
 }  // namespace ffsb

@@ -95,5 +95,30 @@ __device__ __forceinline__ uint4 lds128(const void* p) {
     return v;
 }
 
+// Predicated shared-memory accesses: the compiler turns `if (p) { several stores }` into a
+// divergent branch with a reconvergence barrier; a queue push is cheaper as predicated
+// instructions on the straight-line path.
+__device__ __forceinline__ void sts128_if(bool p, uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "setp.ne.u32 q, %0, 0;\n\t"
+      "@q st.shared.v4.u32 [%1], {%2, %3, %4, %5};\n\t"
+      "}" ::"r"((uint32_t)p),
+      "r"(addr), "r"(x), "r"(y), "r"(z), "r"(w)
+      : "memory");
+}
+
+__device__ __forceinline__ void sts32_if(bool p, uint32_t addr, uint32_t x) {
+    asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "setp.ne.u32 q, %0, 0;\n\t"
+      "@q st.shared.u32 [%1], %2;\n\t"
+      "}" ::"r"((uint32_t)p),
+      "r"(addr), "r"(x)
+      : "memory");
+}
+
 }  // namespace ptx
 }  // namespace ffsb

@@ -58,6 +58,8 @@ struct ThreshArgs {
     float prefilter_k;  // nsig_s^2 * (1 - 1e-4): conservative
     float sig_k;        // nsig_s * (1 - 1e-4)            (fused kernel)
     int thr_floor;      // floor(threshold): v > threshold <=> v > thr_floor for integer v
+    const uint8_t* mcount;  // per pixel: mask-valid pixels in its image-clipped 7x7 window
+    size_t m_pitch;         // (group_info_kernel); 49 <=> window inside the image and fully valid
 };
 
 template <typename PixelT, int KH_, int PPL_, int SR_>
@@ -207,6 +209,79 @@ __device__ __forceinline__ bool resolve_pixel_wide(const ThreshArgs& a, const ui
         if constexpr (sizeof(PixelT) == 2) m += __popc(sel);
     }
     const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    const double md = (double)m, xd = (double)x, yd = (double)y;
+    if (!((int)m >= a.min_count)) return false;
+    if (!(vd > a.threshold)) return false;
+    const double b = __dsub_rn(__dmul_rn(md, vd), xd);
+    const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
+    if (!(b > d)) return false;
+    const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
+                                __dmul_rn(xd, __dsub_rn(md, 1.0)));
+    const double cc =
+      __dmul_rn(__dmul_rn(xd, a.nsig_b), __dsqrt_rn(__dmul_rn(2.0, __dsub_rn(md, 1.0))));
+    return aa > cc;
+}
+
+// Exact test for a pixel whose 7x7 window lies inside the image and is fully mask-valid
+// (mcount == 49): no validity loads, no clipping; the window position only selects which
+// 16-bit halves of the two 16-byte chunks per row take part, and that selection is turned
+// into AND masks once per pixel.  x via IDP.2A, y via 64-bit IMAD.WIDE accumulation.
+// Same fp64 comparison, same operation order as resolve_pixel (standalone.cc:113-174).
+template <typename PixelT, int KH>
+__device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const uint8_t* frame, int col, int row) {
+    const int xs = col - KH;  // >= 0 here
+    const int n_chunks = (int)(a.pitch >> 4);
+    uint32_t m = (2 * KH + 1) * (2 * KH + 1), x = 0;
+    unsigned long long y = 0;
+    // the centre pixel: its line is loaded by the window gather below as well (L1 hit)
+    const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    if constexpr (sizeof(PixelT) == 2) {
+        const int ch0 = xs >> 3, o = xs & 7;
+        const int ch1 = min(ch0 + 1, n_chunks - 1);  // only read when the window reaches it
+        const uint32_t win = 0x7fu << o;             // halves 0..13 of the two chunks
+        uint32_t M[7];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t zz = ((win >> (4 * k)) & 0xfu) * 0x10204080u;
+            M[2 * k] = ptx::prmt(zz, 0u, 0x9988u);
+            if (2 * k + 1 < 7) M[2 * k + 1] = ptx::prmt(zz, 0u, 0xbbaau);
+        }
+#pragma unroll
+        for (int dy = -KH; dy <= KH; ++dy) {
+            const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(row + dy) * a.pitch);
+            const uint4 A = prow[ch0], B = prow[ch1];
+            const uint32_t w[7] = {A.x, A.y, A.z, A.w, B.x, B.y, B.z};
+#pragma unroll
+            for (int q = 0; q < 7; ++q) {
+                const uint32_t t = w[q] & M[q];
+                x = __dp2a_lo(t, 0x0101u, x);
+                const uint32_t lo = t & 0xffffu, hi = t >> 16;
+                y += (unsigned long long)lo * lo;
+                y += (unsigned long long)hi * hi;
+            }
+        }
+    } else {
+        const int ch0 = xs >> 2, o = xs & 3;
+        const int ch2 = min(ch0 + 2, n_chunks - 1);
+        const uint32_t win = 0x7fu << o;  // pixels 0..9 of three chunks
+#pragma unroll
+        for (int dy = -KH; dy <= KH; ++dy) {
+            const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(row + dy) * a.pitch);
+            const uint4 A = prow[ch0], B = prow[ch0 + 1], C = prow[ch2];
+            const uint32_t w[10] = {A.x, A.y, A.z, A.w, B.x, B.y, B.z, B.w, C.x, C.y};
+#pragma unroll
+            for (int q = 0; q < 10; ++q) {
+                // int mm = (mask[k] && src[k] < BIG) ? 1 : 0;   standalone.cc:90
+                const bool in = (win >> q) & 1u;
+                const bool counted = in && w[q] < (1u << 24);
+                const uint32_t pv = counted ? w[q] : 0u;
+                m -= (in && !counted) ? 1u : 0u;
+                x += pv;
+                y += (unsigned long long)pv * pv;
+            }
+        }
+    }
+    const double vd = (double)vc;
     const double md = (double)m, xd = (double)x, yd = (double)y;
     if (!((int)m >= a.min_count)) return false;
     if (!(vd > a.threshold)) return false;

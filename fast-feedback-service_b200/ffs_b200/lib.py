@@ -7,6 +7,7 @@ is no B200: there is no CPU fallback anywhere in this package.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import subprocess
 from pathlib import Path
 
@@ -14,7 +15,8 @@ import numpy as np
 
 _PKG = Path(__file__).resolve().parent
 _ROOT = _PKG.parent
-LIB_PATH = _PKG / "libffs_b200.so"
+# FFS_B200_LIB: developer override to A/B a differently-built copy of the same library
+LIB_PATH = Path(os.environ["FFS_B200_LIB"]) if os.environ.get("FFS_B200_LIB") else _PKG / "libffs_b200.so"
 
 FFS_OK = 0
 ALGO_DISPERSION = 0
