@@ -34,6 +34,9 @@
 
 namespace ffsb {
 
+#ifndef FUSED_DEBUG_MODES
+#define FUSED_DEBUG_MODES 0  // 1: FFS_FUSED_DEBUG=5 (TMA only) is honoured by the streaming loop
+#endif
 #ifndef FUSED_DP2A
 #define FUSED_DP2A 1
 #endif
@@ -71,7 +74,7 @@ struct FusedGeo {
     }
 };
 
-// group info plane: per row, per group of 8 pixels, 2 bytes {validity bits, m_ub}.
+// group info plane: per row, per group of 8 pixels, 2 bytes {validity bits, m_ub | full << 6}.
 // m_ub = max over the group's mask-valid pixels of the number of valid pixels in the
 // image-clipped 7x7 window (standalone.cc:126-130 clipping).
 __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t bits_pitch, int width,
@@ -95,13 +98,17 @@ __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t
         for (int p = 0; p < 8; ++p) m[p] += __popc((b >> (8 + p - 3)) & 0x7fu);
     }
     const uint32_t vb = valid_bits[(size_t)row * bits_pitch + gi];
-    uint32_t mub = 0;
+    uint32_t mub = 0, mlb = 49;
 #pragma unroll
     for (int p = 0; p < 8; ++p)
-        if ((vb >> p) & 1u) mub = max(mub, m[p]);
+        if ((vb >> p) & 1u) {
+            mub = max(mub, m[p]);
+            mlb = min(mlb, m[p]);
+        }
     uint8_t* out = info + (size_t)row * info_pitch + 2 * gi;
     out[0] = (uint8_t)vb;
-    out[1] = (uint8_t)mub;
+    // bit 6: every valid pixel of the group has a full window (inside the image, all 49 valid)
+    out[1] = (uint8_t)(mub | (mlb == 49u ? 0x40u : 0u));
     // per-pixel window counts (extended_stream.cuh): 8 bytes per group, 0 beyond the width
     uint2 mm;
     mm.x = m[0] | (m[1] << 8) | (m[2] << 16) | (m[3] << 24);
@@ -203,10 +210,10 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
             const uint32_t e = gq[qi];
             const uint4 ha = hq[2 * qi], hb = hq[2 * qi + 1];
             const uint32_t hx[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
-            const float rc = rcp_tab[e >> 14];
+            const float rc = rcp_tab[(e >> 14) & 0x7fu];
+            full = ((e >> 20) & 1u) ? 0xffu : 0u;  // group flag: all windows full (m == 49)
             col0 = x0 + (int)(e & 31u) * PPL;
             row = r0 + (int)((e >> 5) & 0x1ffu);
-            const uint2 mc = *reinterpret_cast<const uint2*>(a.mcount + (size_t)row * a.m_pitch + col0);
             uint32_t v[8], vb = 0xffu;
             if constexpr (sizeof(PixelT) == 2) {
                 // masked + clamped centre-row values queued by the streaming loop: a masked pixel
@@ -231,8 +238,6 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
                 uint32_t T = (uint32_t)max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
                 if constexpr (sizeof(PixelT) == 2) T = min(T, G::CLAMP - 1u);
                 bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
-                const uint32_t mj = ((j < 4 ? mc.x : mc.y) >> (8 * (j & 3))) & 0xffu;
-                full |= mj == 49u ? (1u << j) : 0u;
             }
         }
         qn -= n;
@@ -292,8 +297,8 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
     static_assert(SR == 4, "row loop is written for 4-row stages and an 8-row ring");
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ float rcp_tab[64];  // 0.99999 / m_ub
-    for (int t = threadIdx.x; t < 64; t += WARPS * 32) rcp_tab[t] = 0.99999f / (float)max(t, 1);
+    __shared__ float rcp_tab[128];  // 0.99999 / m_ub, indexed by the info byte (m_ub | full << 6)
+    for (int t = threadIdx.x; t < 128; t += WARPS * 32) rcp_tab[t] = 0.99999f / (float)max(t & 63, 1);
     __syncthreads();  // the only block-wide barrier
 
     const int warp = threadIdx.x >> 5;
@@ -365,7 +370,10 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
         const uint8_t* st = stage_base + s * G::STAGE_BYTES;
         uint8_t* rcur = ring_lane + ((g & 1) ? SR * G::RING_ROW_BYTES : 0);
         uint8_t* roth = ring_lane + ((g & 1) ? 0 : SR * G::RING_ROW_BYTES);
-        if (a.force_brute != 5) {  // 5: timing experiment, TMA traffic only
+#if FUSED_DEBUG_MODES
+        if (a.force_brute != 5)   // 5: timing experiment, TMA traffic only
+#endif
+        {
         // The stage body is written in three straight-line phases so that the four rows'
         // dependent chains (LDS -> sums -> SHFL -> sums -> MUFU -> VOTE) interleave.
         // ---- phase A: load, mask, clamp, vertical running sums, ring update ------------------
@@ -480,11 +488,12 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
         }
         }
         // refill the stage we just consumed
+        // Every lane's reads of this stage have completed (their values were consumed above) and
+        // __syncwarp orders them before the elected lane's TMA write, as an mbarrier release /
+        // acquire pair would in a producer-consumer pipeline; no cross-proxy fence is needed for
+        // this read-then-async-write reuse.
         __syncwarp();
-        if (lane == 0 && g + STAGES < n_groups) {
-            ptx::fence_proxy_async();
-            issue(g + STAGES, s);
-        }
+        if (g + STAGES < n_groups && ptx::elect_one()) issue(g + STAGES, s);
         if (++s == STAGES) {
             s = 0;
             phase ^= 1u;

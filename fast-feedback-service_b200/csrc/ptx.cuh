@@ -95,6 +95,20 @@ __device__ __forceinline__ uint4 lds128(const void* p) {
     return v;
 }
 
+// One lane of a converged warp (elect.sync): ptxas recognises the single-thread region and
+// feeds UTMALDG's uniform operands directly, where `lane == 0` costs a lane-serialising loop.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t p;
+    asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, q;\n\t"
+      "}"
+      : "=r"(p));
+    return p != 0;
+}
+
 // Predicated shared-memory accesses: the compiler turns `if (p) { several stores }` into a
 // divergent branch with a reconvergence barrier; a queue push is cheaper as predicated
 // instructions on the straight-line path.
