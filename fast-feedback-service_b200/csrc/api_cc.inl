@@ -71,7 +71,7 @@ static int cc_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     cc_extract_kernel<<<gchunks, 256, 0, st>>>(a);
     cc_link_kernel<<<gpix, 256, 0, st>>>(a);
     cc_reduce_kernel<<<gpix, 256, 0, st>>>(a);
-    cc_finalize_kernel<<<(unsigned)n, 256, 0, st>>>(a);
+    cc_finalize_kernel<<<(unsigned)n, kFinalizeThreads, 0, st>>>(a);
     c->launches += 6;
     FFS_CK(c, cudaGetLastError());
     return FFS_OK;

@@ -375,6 +375,9 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     static bool attr_done[64] = {};
     if (!attr_done[c->p.device & 63]) {
         FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        // occupancy is bounded by shared memory: ask for the whole carve-out
+        FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       cudaSharedmemCarveoutMaxShared));
         attr_done[c->p.device & 63] = true;
     }
     ThreshArgs a{};
@@ -428,6 +431,7 @@ static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
             case 1: return launch_fused_w<PixelT, 1, 2>(c, first_slot, n, st);
             case 2: return launch_fused_w<PixelT, 2, 2>(c, first_slot, n, st);
             case 4: return launch_fused_w<PixelT, 4, 2>(c, first_slot, n, st);
+            case 5: return launch_fused_w<PixelT, 5, 2>(c, first_slot, n, st);
             default: return launch_fused_w<PixelT, 3, 2>(c, first_slot, n, st);
         }
     }

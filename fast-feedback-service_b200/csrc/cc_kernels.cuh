@@ -217,8 +217,11 @@ __global__ void __launch_bounds__(256) cc_reduce_kernel(const CCArgs a) {
 }
 
 // K6: ordered compaction of roots into spot records + per-frame counters.
-// grid (n_frames), 256 threads; loops over the frame's compact list.
-__global__ void __launch_bounds__(256) cc_finalize_kernel(const CCArgs a) {
+// grid (n_frames), 1024 threads; loops over the frame's compact list 1024 entries at a time.
+// A root's rank is the number of roots before it in list order: ballot + popc inside the warp,
+// one shared-memory pass over the 32 warp totals across warps.
+constexpr int kFinalizeThreads = 1024;
+__global__ void __launch_bounds__(kFinalizeThreads) cc_finalize_kernel(const CCArgs a) {
     const int z = a.slot0 + blockIdx.x;
     uint32_t* cnt = a.counts + (size_t)z * CNT_N;
     const uint32_t S = cnt[CNT_STRONG];
@@ -227,30 +230,66 @@ __global__ void __launch_bounds__(256) cc_finalize_kernel(const CCArgs a) {
     const SpotAcc* acc = a.acc + (size_t)z * a.cap;
     ffs_spot* spots = a.spots + (size_t)z * a.cap_spots;
     const uint32_t W = (uint32_t)a.width;
-    uint32_t running = 0;
-    for (uint32_t base = 0; base < S; base += 256) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ uint32_t warp_roots[2][32];  // double-buffered: one barrier per round
+    __shared__ uint32_t totals[3];
+    if (threadIdx.x < 3) totals[threadIdx.x] = 0;
+    uint32_t running = 0, n_total = 0, n_strong = 0, n_filtered = 0;
+    int buf = 0;
+    for (uint32_t base = 0; base < S; base += kFinalizeThreads, buf ^= 1) {
         const uint32_t i = base + threadIdx.x;
         const bool is_root = i < S && par[i] == i;
-        uint32_t tot;
-        const uint32_t rank = running + block_exclusive_scan_256(is_root ? 1u : 0u, &tot);
-        running += tot;
+        const unsigned ball = __ballot_sync(0xffffffffu, is_root);
+        if (lane == 0) warp_roots[buf][warp] = __popc(ball);
+        // start the root's loads before the barrier
+        SpotAcc r;
+        uint32_t first = 0;
         if (is_root) {
-            const SpotAcc r = acc[i];
+            r = acc[i];
+            first = idx[i];
+        }
+        __syncthreads();
+        const uint32_t wr = warp_roots[buf][lane];
+        uint32_t before = lane < warp ? wr : 0u, all = wr;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            before += __shfl_xor_sync(0xffffffffu, before, off);
+            all += __shfl_xor_sync(0xffffffffu, all, off);
+        }
+        if (is_root) {
+            const uint32_t rank = running + before + __popc(ball & ((1u << lane) - 1u));
             const uint32_t pid = ~(uint32_t)(r.peak & 0xffffffffu);
             const uint32_t pk = idx[pid];
             ffs_spot s;
-            acc_to_spot(r, (uint64_t)idx[i], pk % W, pk / W, 0, &s);
+            acc_to_spot(r, (uint64_t)first, pk % W, pk / W, 0, &s);
             if (rank < a.cap_spots) spots[rank] = s;
             // get_boxes keeps num_pixels >= min_spot_size (connected_components.cc:121-131);
             // filter_reflections then drops distance > max_sep (:207-236)
             if (!(a.min_spot_size > 0 && s.num_pixels < a.min_spot_size)) {
-                atomicAdd(&cnt[CNT_SPOTS_TOTAL], 1u);
-                atomicAdd(&cnt[CNT_STRONG_FILTERED], s.num_pixels);
-                if (!(a.max_sep > 0 && s.peak_centroid_distance > a.max_sep)) atomicAdd(&cnt[CNT_SPOTS_FILTERED], 1u);
+                ++n_total;
+                n_strong += s.num_pixels;
+                if (!(a.max_sep > 0 && s.peak_centroid_distance > a.max_sep)) ++n_filtered;
             }
         }
+        running += all;
     }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        n_total += __shfl_xor_sync(0xffffffffu, n_total, off);
+        n_strong += __shfl_xor_sync(0xffffffffu, n_strong, off);
+        n_filtered += __shfl_xor_sync(0xffffffffu, n_filtered, off);
+    }
+    __syncthreads();  // totals[] initialised
+    if (lane == 0 && (n_total | n_strong | n_filtered)) {
+        atomicAdd(&totals[0], n_total);
+        atomicAdd(&totals[1], n_strong);
+        atomicAdd(&totals[2], n_filtered);
+    }
+    __syncthreads();
     if (threadIdx.x == 0) {
+        cnt[CNT_SPOTS_TOTAL] = totals[0];
+        cnt[CNT_STRONG_FILTERED] = totals[1];
+        cnt[CNT_SPOTS_FILTERED] = totals[2];
         cnt[CNT_COMPONENTS] = running;
         if (running > a.cap_spots) cnt[CNT_STATUS] = (uint32_t)FFS_ERR_CAPACITY;
     }

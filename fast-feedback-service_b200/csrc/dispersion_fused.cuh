@@ -63,10 +63,11 @@ struct FusedGeo {
     static constexpr int RING_ROW_BYTES = 32 * 16;
     static constexpr int RING_BYTES = RING_ROWS * RING_ROW_BYTES;
     static constexpr int GQ_CAP = 96;        // pending candidate groups (< 32 + 2 rows * 30)
-    static constexpr int PQ_CAP = 288;       // pending candidate pixels (< 32 + 32 * 8)
+    static constexpr int PQ_CAP = 320;       // pending candidate pixels, both kinds (< 32 + 32 + 32 * 8)
     // per queued group: 4 B meta + 32 B window sums + 16 B clamped centre-row words
-    // plus two pixel queues: windows that are fully valid (fast exact test) / all others
-    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + 2 * PQ_CAP * 4;
+    // plus one double-ended pixel queue: pixels whose window is fully valid (fast exact test)
+    // grow from the bottom, all others from the top
+    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + PQ_CAP * 4;
     static_assert(RING_ROWS > 2 * KH, "ring must hold the 7-row window");
     static_assert(IMG_STAGE_BYTES % 128 == 0 && QUEUE_BYTES % 128 == 0, "TMA destination alignment");
     __host__ __device__ static constexpr int smem_per_warp(int stages) {
@@ -178,8 +179,8 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
     uint32_t* gq = reinterpret_cast<uint32_t*>(qbase);
     uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);
     uint4* cq = hq + 2 * G::GQ_CAP;
-    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);  // pixels with a full 7x7 window
-    uint32_t* pg = pq + G::PQ_CAP;                               // pixels near the mask / the edge
+    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);  // [0, pqn): pixels with a full 7x7 window
+    uint32_t* pg = pq + G::PQ_CAP - 1;                           // pg[-k], k < pgn: pixels near the mask / the edge
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
     const uint8_t* valid = a.valid_bits;
     const float sk = a.sig_k;
@@ -261,7 +262,7 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         for (uint32_t b = bg; b;) {
             const int j = __ffs(b) - 1;
             b &= b - 1;
-            pg[pos++] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
+            pg[-(pos++)] = (uint32_t)(col0 + j) | ((uint32_t)row << 13);
         }
         const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
         pqn += (int)(tot & 0xffffu);
@@ -273,13 +274,13 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         }
         while (pgn >= 32) {
             pgn -= 32;
-            resolve_any(pg[pgn + lane]);
+            resolve_any(pg[-(pgn + lane)]);
         }
         __syncwarp();
     }
     if (flush_all) {
         if (lane < pqn) resolve_full(pq[lane]);
-        if (lane < pgn) resolve_any(pg[lane]);
+        if (lane < pgn) resolve_any(pg[-lane]);
         pqn = pgn = 0;
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);

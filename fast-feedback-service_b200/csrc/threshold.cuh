@@ -249,7 +249,10 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
 #pragma unroll
         for (int dy = -KH; dy <= KH; ++dy) {
             const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(row + dy) * a.pitch);
-            const uint4 A = prow[ch0], B = prow[ch1];
+            // the gather is bound by L1 wavefronts (one per lane and load): skip the second
+            // chunk when the 7 pixels fit into the first (window offset 0 or 1)
+            const uint4 A = prow[ch0];
+            const uint4 B = o > 1 ? prow[ch1] : make_uint4(0, 0, 0, 0);
             const uint32_t w[7] = {A.x, A.y, A.z, A.w, B.x, B.y, B.z};
 #pragma unroll
             for (int q = 0; q < 7; ++q) {
