@@ -299,7 +299,13 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ float rcp_tab[128];  // 0.99999 / m_ub, indexed by the info byte (m_ub | full << 6)
+    // The out-of-line resolve path takes the arguments by pointer; a pointer to the kernel
+    // parameter turns every field access into a generic load from the parameter window
+    // (long-scoreboard latency on each call), a shared-memory copy is one LDS away.
+    __shared__ ThreshArgs sa;
     for (int t = threadIdx.x; t < 128; t += WARPS * 32) rcp_tab[t] = 0.99999f / (float)max(t & 63, 1);
+    for (int t = threadIdx.x; t < (int)(sizeof(ThreshArgs) / 4); t += WARPS * 32)
+        reinterpret_cast<uint32_t*>(&sa)[t] = reinterpret_cast<const uint32_t*>(&a)[t];
     __syncthreads();  // the only block-wide barrier
 
     const int warp = threadIdx.x >> 5;
@@ -366,8 +372,9 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
 
     int s = 0;
     uint32_t phase = 0;
+    bool ready = false;  // the next stage's barrier was already seen complete (polled early)
     for (int g = 0; g < n_groups; ++g) {
-        ptx::mbar_wait(bars + s, phase);
+        if (!ready) ptx::mbar_wait(bars + s, phase);
         const uint8_t* st = stage_base + s * G::STAGE_BYTES;
         uint8_t* rcur = ring_lane + ((g & 1) ? SR * G::RING_ROW_BYTES : 0);
         uint8_t* roth = ring_lane + ((g & 1) ? 0 : SR * G::RING_ROW_BYTES);
@@ -463,6 +470,11 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             ball[u] = __ballot_sync(0xffffffffu,
                                     out_lane && vmc[u] > (uint32_t)T && i >= 2 * KH && out_row < row_end);
         }
+        // poll the next stage's barrier now; the answer arrives while phase C runs
+        {
+            const int sn = (s + 1 == STAGES) ? 0 : s + 1;
+            ready = g + 1 < n_groups && ptx::mbar_try_wait(bars + sn, (s + 1 == STAGES) ? phase ^ 1u : phase);
+        }
         // ---- phase C: queue the passing groups (predicated stores, no divergence); resolve
         // when 32 are pending -- checked every two rows, which GQ_CAP allows for ----------------
         const uint32_t gq_s = ptx::smem_u32(gq), hq_s = ptx::smem_u32(hq), cq_s = ptx::smem_u32(cq);
@@ -480,7 +492,7 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             if ((u & 1) && qn >= 32) {
                 __syncwarp();
                 do {
-                    const uint32_t st2 = fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z,
+                    const uint32_t st2 = fused_resolve<PixelT>(&sa, qbase, rcp_tab, x0, r0, z,
                                                                (uint32_t)qn | pstate, 32, false);
                     qn = st2 & 0xff;
                     pstate = st2 & ~0xffu;
@@ -502,7 +514,7 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
     }
     __syncwarp();
     if (qn > 0 || pstate)
-        fused_resolve<PixelT>(&a, qbase, rcp_tab, x0, r0, z, (uint32_t)qn | pstate, qn, true);
+        fused_resolve<PixelT>(&sa, qbase, rcp_tab, x0, r0, z, (uint32_t)qn | pstate, qn, true);
 }
 
 }  // namespace ffsb
