@@ -171,6 +171,7 @@ __global__ void __launch_bounds__(WARPS * 32)
     const bool store_lane = out_lane && group < (int)a.strong_pitch;
     uint8_t* dplane = reinterpret_cast<uint8_t*>(a.strong_bits) + (size_t)z * a.strong_frame_stride;
     int qn = 0, pqn = 0;
+    unsigned n_set = 0;
 
     uint32_t V[4] = {0, 0, 0, 0};                  // packed column sums of x over the last 7 rows
     uint32_t Vy[8] = {0, 0, 0, 0, 0, 0, 0, 0};     // column sums of the squares
@@ -248,18 +249,7 @@ __global__ void __launch_bounds__(WARPS * 32)
                 const uint32_t l3 = __shfl_up_sync(0xffffffffu, V[3], 1);
                 const uint32_t rr0 = __shfl_down_sync(0xffffffffu, V[0], 1);
                 const uint32_t rr1 = __shfl_down_sync(0xffffffffu, V[1], 1);
-                uint32_t Ex[14], Ey[14];
-                Ex[0] = l2 >> 16;
-                Ex[1] = l3 & 0xffffu;
-                Ex[2] = l3 >> 16;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    Ex[3 + 2 * k] = V[k] & 0xffffu;
-                    Ex[4 + 2 * k] = V[k] >> 16;
-                }
-                Ex[11] = rr0 & 0xffffu;
-                Ex[12] = rr0 >> 16;
-                Ex[13] = rr1 & 0xffffu;
+                uint32_t Ey[14];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     Ey[k] = __shfl_up_sync(0xffffffffu, Vy[5 + k], 1);
@@ -268,13 +258,24 @@ __global__ void __launch_bounds__(WARPS * 32)
 #pragma unroll
                 for (int k = 0; k < 8; ++k) Ey[3 + k] = Vy[k];
                 uint32_t Hx[8], Hy[8];
-                Hx[0] = Ex[0] + Ex[1] + Ex[2] + Ex[3] + Ex[4] + Ex[5] + Ex[6];
+                {   // 7-tap sums of the packed 16-bit column sums with IDP.2A (see dispersion_fused.cuh)
+                    constexpr uint32_t LO = 0x0001u, HI = 0x0100u, BOTH = 0x0101u;
+                    const uint32_t a23 = __dp2a_lo(V[0], BOTH, __dp2a_lo(V[1], BOTH, 0u));
+                    const uint32_t a45 = __dp2a_lo(V[2], BOTH, __dp2a_lo(V[3], BOTH, 0u));
+                    const uint32_t t1 = __dp2a_lo(l3, BOTH, a23), t2 = __dp2a_lo(V[2], BOTH, a23);
+                    const uint32_t t3 = __dp2a_lo(V[1], BOTH, a45), t4 = __dp2a_lo(rr0, BOTH, a45);
+                    Hx[0] = __dp2a_lo(l2, HI, t1);
+                    Hx[1] = __dp2a_lo(V[2], LO, t1);
+                    Hx[2] = __dp2a_lo(l3, HI, t2);
+                    Hx[3] = __dp2a_lo(V[3], LO, t2);
+                    Hx[4] = __dp2a_lo(V[0], HI, t3);
+                    Hx[5] = __dp2a_lo(rr0, LO, t3);
+                    Hx[6] = __dp2a_lo(V[1], HI, t4);
+                    Hx[7] = __dp2a_lo(rr1, LO, t4);
+                }
                 Hy[0] = Ey[0] + Ey[1] + Ey[2] + Ey[3] + Ey[4] + Ey[5] + Ey[6];
 #pragma unroll
-                for (int j = 1; j < 8; ++j) {
-                    Hx[j] = Hx[j - 1] + Ex[j + 6] - Ex[j - 1];
-                    Hy[j] = Hy[j - 1] + Ey[j + 6] - Ey[j - 1];
-                }
+                for (int j = 1; j < 8; ++j) Hy[j] = Hy[j - 1] + Ey[j + 6] - Ey[j - 1];
                 // ---- per-pixel test in fp32 with an error bound --------------------------------------
                 const uint2 mw = *reinterpret_cast<const uint2*>(st + pm_off + u * E::M_ROW_BYTES);
                 const uint32_t vb = hi3 & 0xffu;  // validity of the centre row's pixels
@@ -297,8 +298,7 @@ __global__ void __launch_bounds__(WARPS * 32)
                     border = vb;
                 }
                 if (store_lane) dplane[(size_t)out_row * a.strong_pitch + group] = (uint8_t)dbits;
-                const unsigned cnt = __popc(out_lane ? dbits : 0u);
-                if (cnt) atomicAdd(a.strong_count + z, cnt);
+                n_set += __popc(out_lane ? dbits : 0u);  // one atomic per task, at the end
                 const bool push = out_lane && border != 0;
                 const unsigned ball = __ballot_sync(0xffffffffu, push);
                 if (ball) {
@@ -317,17 +317,16 @@ __global__ void __launch_bounds__(WARPS * 32)
             }
             hi3 = hi2; hi2 = hi1; hi1 = info;
         }
-        __syncwarp();
-        if (lane == 0 && g + STAGES < n_groups) {
-            ptx::fence_proxy_async();
-            issue(g + STAGES, s);
-        }
+        __syncwarp();  // see dispersion_fused.cuh on this read-then-async-write reuse
+        if (g + STAGES < n_groups && ptx::elect_one()) issue(g + STAGES, s);
         if (++s == STAGES) {
             s = 0;
             phase ^= 1u;
         }
     }
     __syncwarp();
+    for (int off = 16; off > 0; off >>= 1) n_set += __shfl_down_sync(0xffffffffu, n_set, off);
+    if (lane == 0 && n_set) atomicAdd(a.strong_count + z, n_set);
     if (qn > 0 || pqn > 0)
         ext_resolve<PixelT>(&a, gq, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
 }
