@@ -15,6 +15,7 @@ extern "C" int ffs_sweep_begin(ffs_ctx* c, uint64_t max_frames) {
     c->sweep_plane[0].clear();
     c->sweep_plane[1].clear();
     c->sweep_sums.clear();
+    c->sweep_moments.clear();
     return FFS_OK;
 }
 
@@ -73,11 +74,11 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
              *d_n = nullptr;
     SpotAcc* d_acc = nullptr;
     ffs_spot* d_spots = nullptr;
-    unsigned long long* d_sums = nullptr;
+    unsigned long long *d_sums = nullptr, *d_mom = nullptr;
     int rc = FFS_OK;
     auto cleanup = [&]() {
         cudaFree(d_fo); cudaFree(d_idx); cudaFree(d_val); cudaFree(d_z); cudaFree(d_par);
-        cudaFree(d_rank); cudaFree(d_n); cudaFree(d_acc); cudaFree(d_spots); cudaFree(d_sums);
+        cudaFree(d_rank); cudaFree(d_n); cudaFree(d_acc); cudaFree(d_spots); cudaFree(d_sums); cudaFree(d_mom);
     };
 #define SWEEP_CK(call)                                                        \
     do {                                                                      \
@@ -98,6 +99,8 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     SWEEP_CK(cudaMalloc(&d_acc, total * sizeof(SpotAcc)));
     SWEEP_CK(cudaMalloc(&d_spots, total * sizeof(ffs_spot)));
     SWEEP_CK(cudaMalloc(&d_sums, total * 4 * sizeof(unsigned long long)));
+    SWEEP_CK(cudaMalloc(&d_mom, total * 4 * sizeof(unsigned long long)));
+    SWEEP_CK(cudaMemsetAsync(d_mom, 0, total * 4 * sizeof(unsigned long long), c->stream));
     SWEEP_CK(cudaMemcpy(d_fo, fo.data(), (nz + 1) * 4, cudaMemcpyHostToDevice));
     SWEEP_CK(cudaMemcpy(d_idx, idx.data(), total * 4, cudaMemcpyHostToDevice));
     SWEEP_CK(cudaMemcpy(d_val, val.data(), total * 4, cudaMemcpyHostToDevice));
@@ -108,7 +111,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     a.n_slices = (uint32_t)nz;
     a.total = (uint32_t)total;
     a.fo = d_fo; a.idx = d_idx; a.val = d_val; a.zarr = d_z;
-    a.parent = d_par; a.rank = d_rank; a.acc = d_acc; a.spots = d_spots; a.sums = d_sums;
+    a.parent = d_par; a.rank = d_rank; a.acc = d_acc; a.spots = d_spots; a.sums = d_sums; a.moments = d_mom;
     a.cap_spots = (uint32_t)total;
     a.n_components = d_n;
     a.row_wrap = c->p.cc_row_wrap;
@@ -117,7 +120,8 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     cc3_link_kernel<<<grid, 256, 0, c->stream>>>(a);
     cc3_reduce_kernel<<<grid, 256, 0, c->stream>>>(a);
     cc3_finalize_kernel<<<1, 256, 0, c->stream>>>(a);
-    c->launches += 4;
+    cc3_moments_kernel<<<grid, 256, 0, c->stream>>>(a);
+    c->launches += 5;
     SWEEP_CK(cudaGetLastError());
     uint32_t n = 0;
     SWEEP_CK(cudaMemcpyAsync(&n, d_n, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -130,6 +134,8 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     if (n) SWEEP_CK(cudaMemcpy(out, d_spots, sizeof(ffs_spot) * n, cudaMemcpyDeviceToHost));
     c->sweep_sums.assign((size_t)n * 4, 0);
     if (n) SWEEP_CK(cudaMemcpy(c->sweep_sums.data(), d_sums, sizeof(uint64_t) * 4 * n, cudaMemcpyDeviceToHost));
+    c->sweep_moments.assign((size_t)n * 4, 0);
+    if (n) SWEEP_CK(cudaMemcpy(c->sweep_moments.data(), d_mom, sizeof(uint64_t) * 4 * n, cudaMemcpyDeviceToHost));
     // boundary planes for slab-sharded sweeps: {linear index, component rank} of the first
     // and last slice
     {
@@ -173,5 +179,68 @@ extern "C" int ffs_sweep_export_sums(ffs_ctx* c, uint64_t** sums, size_t* n_spot
     *sums = (uint64_t*)malloc(c->sweep_sums.size() * sizeof(uint64_t));
     if (!*sums) return FFS_ERR_NOMEM;
     memcpy(*sums, c->sweep_sums.data(), c->sweep_sums.size() * sizeof(uint64_t));
+    return FFS_OK;
+}
+
+extern "C" int ffs_sweep_export_moments(ffs_ctx* c, uint64_t** moments, size_t* n_spots) {
+    if (!c || !moments || !n_spots) return FFS_ERR_ARG;
+    *n_spots = c->sweep_moments.size() / 4;
+    *moments = nullptr;
+    if (c->sweep_moments.empty()) return FFS_OK;
+    *moments = (uint64_t*)malloc(c->sweep_moments.size() * sizeof(uint64_t));
+    if (!*moments) return FFS_ERR_NOMEM;
+    memcpy(*moments, c->sweep_moments.data(), c->sweep_moments.size() * sizeof(uint64_t));
+    return FFS_OK;
+}
+
+extern "C" int ffs_kabsch_variances(ffs_ctx* c, const ffs_kabsch_geometry* g, const ffs_spot* spots,
+                                    const uint64_t* sums, const uint64_t* moments, size_t n,
+                                    double* sigma_b, double* sigma_m, int32_t* depth) {
+    if (!c || !g || (n && (!spots || !sums || !moments))) return FFS_ERR_ARG;
+    if (n == 0) return FFS_OK;
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    ffs_spot* d_spots = nullptr;
+    unsigned long long *d_sums = nullptr, *d_mom = nullptr;
+    double *d_b = nullptr, *d_m = nullptr;
+    int32_t* d_d = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(d_spots); cudaFree(d_sums); cudaFree(d_mom); cudaFree(d_b); cudaFree(d_m); cudaFree(d_d);
+    };
+#define KAB_CK(call)                                                          \
+    do {                                                                      \
+        cudaError_t e__ = (call);                                             \
+        if (e__ != cudaSuccess) {                                             \
+            c->err = std::string(#call) + ": " + cudaGetErrorString(e__);     \
+            cleanup();                                                        \
+            return FFS_ERR_CUDA;                                              \
+        }                                                                     \
+    } while (0)
+    KAB_CK(cudaMalloc(&d_spots, n * sizeof(ffs_spot)));
+    KAB_CK(cudaMalloc(&d_sums, n * 4 * sizeof(uint64_t)));
+    KAB_CK(cudaMalloc(&d_mom, n * 4 * sizeof(uint64_t)));
+    KAB_CK(cudaMalloc(&d_b, n * sizeof(double)));
+    KAB_CK(cudaMalloc(&d_m, n * sizeof(double)));
+    KAB_CK(cudaMalloc(&d_d, n * sizeof(int32_t)));
+    KAB_CK(cudaMemcpyAsync(d_spots, spots, n * sizeof(ffs_spot), cudaMemcpyHostToDevice, c->stream));
+    KAB_CK(cudaMemcpyAsync(d_sums, sums, n * 4 * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    KAB_CK(cudaMemcpyAsync(d_mom, moments, n * 4 * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    KabschArgs a{};
+    a.g = *g;
+    a.spots = d_spots;
+    a.sums = d_sums;
+    a.moments = d_mom;
+    a.n = (uint32_t)n;
+    a.sigma_b = d_b;
+    a.sigma_m = d_m;
+    a.depth = d_d;
+    kabsch_kernel<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(a);
+    c->launches++;
+    KAB_CK(cudaGetLastError());
+    if (sigma_b) KAB_CK(cudaMemcpyAsync(sigma_b, d_b, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sigma_m) KAB_CK(cudaMemcpyAsync(sigma_m, d_m, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (depth) KAB_CK(cudaMemcpyAsync(depth, d_d, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    KAB_CK(cudaStreamSynchronize(c->stream));
+#undef KAB_CK
+    cleanup();
     return FFS_OK;
 }

@@ -175,11 +175,53 @@
             return 1;
         }
         printf("Calculated %zu spots\n", n3);
+        // Kabsch-space variances of every component (spotfinder.cc:1152-1196), evaluated before
+        // the filter compacts the array; the kept spots are picked out by label afterwards
+        std::vector<double> var_b(n3), var_m(n3);
+        std::vector<int32_t> depth(n3);
+        std::vector<uint64_t> labels3(n3);
+        for (size_t i = 0; i < n3; ++i) labels3[i] = s3[i].label;
+        if (n3) {
+            uint64_t *sums = nullptr, *moments = nullptr;
+            size_t ns = 0, nm = 0;
+            ffs_kabsch_geometry kg{};
+            kg.distance_mm = det.distance * 1000;
+            kg.beam_center_x_px = det.beam_center_x;
+            kg.beam_center_y_px = det.beam_center_y;
+            kg.pixel_size_x_mm = det.pixel_size_x * 1000;
+            kg.pixel_size_y_mm = det.pixel_size_y * 1000;
+            kg.wavelength = wavelength;
+            kg.oscillation_width_deg = oscillation_width;
+            if (ffs_sweep_export_sums(ctx, &sums, &ns) != FFS_OK || ffs_sweep_export_moments(ctx, &moments, &nm) != FFS_OK ||
+                ns != n3 || nm != n3 ||
+                ffs_kabsch_variances(ctx, &kg, s3, sums, moments, n3, var_b.data(), var_m.data(), depth.data()) != FFS_OK) {
+                printf("Error: spot variance calculation failed: %s\n", ffs_last_error(ctx));
+                return 1;
+            }
+            ffs_free(sums);
+            ffs_free(moments);
+        }
         size_t rs = 0, rp = 0;
         const size_t kept = ffs_filter_spots(s3, n3, args.min_spot_size_3d, args.max_peak_centroid_separation, &rs, &rp);
         if (rs > 0) printf("Filtered %zu spots with size < %u pixels\n", rs, args.min_spot_size_3d);
         if (rp > 0) printf("Filtered %zu spots with peak-centroid distance > %s\n", rp, shortest(args.max_peak_centroid_separation).c_str());
         printf("Found %zu spots\n", kept);
+        {   // estimated global values over the kept reflections (spotfinder.cc:1180-1212)
+            double sum_b = 0, sum_m = 0;
+            size_t n_m = 0, j = 0;
+            for (size_t i = 0; i < kept; ++i) {
+                while (j < n3 && labels3[j] != s3[i].label) ++j;  // the filter is stable
+                if (j == n3) break;
+                sum_b += var_b[j];
+                if (depth[j] >= 5) {  // min_bbox_depth
+                    sum_m += var_m[j];
+                    ++n_m;
+                }
+            }
+            const double rad_to_deg = 180.0 / M_PI;
+            if (kept) printf("Estimated sigma_b (degrees): %.6f\n", std::sqrt(sum_b / kept) * rad_to_deg);
+            if (n_m) printf("Estimated sigma_m (degrees): %.6f, calculated on %zu spots\n", std::sqrt(sum_m / n_m) * rad_to_deg, n_m);
+        }
         if (args.writeout) {
             std::ofstream out("3d_reflections.txt");
             for (size_t i = 0; i < kept; ++i)

@@ -60,6 +60,17 @@ class Spot(C.Structure):
 SPOT_DTYPE = np.dtype(Spot)
 
 
+class KabschGeometry(C.Structure):
+    """ffs_kabsch_geometry: what spotfinder.cc:1157-1168 builds its Panel / s0 / Scan from."""
+    _fields_ = [
+        ("distance_mm", C.c_double),
+        ("beam_center_x_px", C.c_double), ("beam_center_y_px", C.c_double),
+        ("pixel_size_x_mm", C.c_double), ("pixel_size_y_mm", C.c_double),
+        ("wavelength", C.c_double),
+        ("oscillation_width_deg", C.c_double),
+    ]
+
+
 class FrameResult(C.Structure):
     _fields_ = [
         ("frame_id", C.c_uint64),
@@ -109,6 +120,8 @@ SYMBOLS = {
     "ffs_sweep_finish": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_plane": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_sums": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_sweep_export_moments": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_kabsch_variances": (_i, [_vp, C.POINTER(KabschGeometry), _vp, _vp, _vp, _sz, _vp, _vp, _vp]),
     "ffs_free": (None, [_vp]),
     "ffs_filter_spots": (_sz, [_vp, _sz, C.c_uint32, C.c_float, C.POINTER(_sz), C.POINTER(_sz)]),
     "ffs_kernel_launches": (C.c_uint64, [_vp]),

@@ -288,3 +288,34 @@ class Spotfinder:
         out = np.frombuffer(buf, dtype=np.uint64).reshape(-1, 4).copy()
         self._L.ffs_free(ptr)
         return out
+
+    def sweep_export_moments(self) -> np.ndarray:
+        """(n, 4) uint64 bbox-relative second moments {I u^2, I v^2, I u v, I w^2} of the last
+        sweep_finish (u = x - x_min, v = y - y_min, w = z - z_min)."""
+        ptr, n = C.c_void_p(), C.c_size_t(0)
+        self._ck(self._L.ffs_sweep_export_moments(self._ctx, C.byref(ptr), C.byref(n)), "ffs_sweep_export_moments")
+        if not n.value:
+            return np.zeros((0, 4), np.uint64)
+        buf = (C.c_uint64 * (4 * n.value)).from_address(ptr.value)
+        out = np.frombuffer(buf, dtype=np.uint64).reshape(-1, 4).copy()
+        self._L.ffs_free(ptr)
+        return out
+
+    def kabsch_variances(self, geometry: dict, spots: np.ndarray, sums: np.ndarray, moments: np.ndarray):
+        """(sigma_b_variance, sigma_m_variance, bbox_depth) per spot -- the tuple
+        Reflection3D::variances_in_kabsch_space returns (connected_components.cc:159-203),
+        evaluated on the device.  geometry keys: distance_mm, beam_center_x_px, beam_center_y_px,
+        pixel_size_x_mm, pixel_size_y_mm, wavelength, oscillation_width_deg."""
+        from .lib import KabschGeometry
+        g = KabschGeometry(**{k: float(v) for k, v in geometry.items()})
+        spots = np.ascontiguousarray(spots, dtype=SPOT_DTYPE)
+        sums = np.ascontiguousarray(sums, dtype=np.uint64).reshape(-1, 4)
+        moments = np.ascontiguousarray(moments, dtype=np.uint64).reshape(-1, 4)
+        n = len(spots)
+        if len(sums) != n or len(moments) != n:
+            raise ValueError("spots, sums and moments must describe the same spots")
+        sb, sm, depth = np.zeros(n, np.float64), np.zeros(n, np.float64), np.zeros(n, np.int32)
+        self._ck(self._L.ffs_kabsch_variances(self._ctx, C.byref(g), spots.ctypes.data, sums.ctypes.data,
+                                              moments.ctypes.data, n, sb.ctypes.data, sm.ctypes.data,
+                                              depth.ctypes.data), "ffs_kabsch_variances")
+        return sb, sm, depth

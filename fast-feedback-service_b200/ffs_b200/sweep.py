@@ -31,6 +31,7 @@ class SlabResult:
     sums: np.ndarray        # (n, 4) uint64: sum I, (2x+1)I, (2y+1)I, (2z+1)I  (z local)
     first: np.ndarray       # (k, 2) uint32 {linear index, component} of the slab's first frame
     last: np.ndarray        # (k, 2) uint32 of its last frame
+    moments: np.ndarray | None = None  # (n, 4) uint64: sum I u^2, I v^2, I u v, I w^2 about the box minimum
 
 
 def slab_bounds(n_frames: int, world: int, rank: int) -> tuple[int, int]:
@@ -45,22 +46,63 @@ def _find(parent, i):
     return i
 
 
-def merge_slabs(slabs: list[SlabResult], width: int, height: int) -> np.ndarray:
-    """All 3D components of the sweep (unfiltered, canonical order) from per-slab results."""
+def _absolute_moments(spots, sums, moments):
+    """bbox-relative second moments -> moments about the origin (exact Python integers).
+    sum I x^2 = sum I u^2 + 2 a sum I u + a^2 sum I, with sum I u = sum I x - a sum I, a = x_min."""
+    out = np.zeros((len(spots), 4), dtype=object)
+    for i in range(len(spots)):
+        S0 = int(sums[i, 0])
+        Ix, Iy, Iz = ((int(sums[i, k]) - S0) // 2 for k in (1, 2, 3))
+        a, b, c = int(spots["x_min"][i]), int(spots["y_min"][i]), int(spots["z_min"][i])
+        Iu, Iv, Iw = Ix - a * S0, Iy - b * S0, Iz - c * S0
+        m = [int(v) for v in moments[i]]
+        out[i, 0] = m[0] + 2 * a * Iu + a * a * S0
+        out[i, 1] = m[1] + 2 * b * Iv + b * b * S0
+        out[i, 2] = m[2] + a * Iv + b * Iu + a * b * S0
+        out[i, 3] = m[3] + 2 * c * Iw + c * c * S0
+    return out
+
+
+def _relative_moments(spots, sums, absm):
+    """Inverse of _absolute_moments for the (merged) bounding boxes in `spots`."""
+    out = np.zeros((len(spots), 4), dtype=np.uint64)
+    for i in range(len(spots)):
+        S0 = int(sums[i, 0])
+        Ix, Iy, Iz = ((int(sums[i, k]) - S0) // 2 for k in (1, 2, 3))
+        a, b, c = int(spots["x_min"][i]), int(spots["y_min"][i]), int(spots["z_min"][i])
+        out[i, 0] = int(absm[i, 0]) - 2 * a * Ix + a * a * S0
+        out[i, 1] = int(absm[i, 1]) - 2 * b * Iy + b * b * S0
+        out[i, 2] = int(absm[i, 2]) - a * Iy - b * Ix + a * b * S0
+        out[i, 3] = int(absm[i, 3]) - 2 * c * Iz + c * c * S0
+    return out
+
+
+def merge_slabs(slabs: list[SlabResult], width: int, height: int, with_sums: bool = False):
+    """All 3D components of the sweep (unfiltered, canonical order) from per-slab results.
+    with_sums: also return the merged exact sums (n, 4) and, if every slab carries them, the
+    merged bbox-relative second moments (n, 4) -- the inputs of Spotfinder.kabsch_variances."""
     slabs = sorted(slabs, key=lambda s: s.z0)
     px = width * height
     offs = np.cumsum([0] + [len(s.spots) for s in slabs])
     n = int(offs[-1])
     if n == 0:
-        return np.zeros(0, SPOT_DTYPE)
+        empty = np.zeros(0, SPOT_DTYPE)
+        return (empty, np.zeros((0, 4), np.uint64), np.zeros((0, 4), np.uint64)) if with_sums else empty
     spots = np.concatenate([s.spots for s in slabs]).copy()
     sums = np.concatenate([s.sums.reshape(-1, 4) for s in slabs]).astype(object)  # exact big ints
+    have_moments = all(s.moments is not None for s in slabs)
+    absm = None
+    if have_moments:  # about the origin with slab-local z, so that they simply add
+        absm = np.concatenate([_absolute_moments(s.spots, s.sums.reshape(-1, 4), s.moments.reshape(-1, 4))
+                               for s in slabs])
     # globalise z (slab-local -> sweep): bbox, peak, label, and sum (2z+1)I += 2*z0*sum I
     for s, a, b in zip(slabs, offs[:-1], offs[1:]):
         spots["z_min"][a:b] += s.z0
         spots["z_max"][a:b] += s.z0
         spots["peak_z"][a:b] += s.z0
         spots["label"][a:b] += np.uint64(s.z0 * px)
+        if absm is not None:  # sum I (z + z0)^2, with sum I z = (sum (2z+1) I - sum I) / 2 still slab-local
+            absm[a:b, 3] += 2 * s.z0 * ((sums[a:b, 3] - sums[a:b, 0]) // 2) + s.z0 * s.z0 * sums[a:b, 0]
         sums[a:b, 3] += 2 * s.z0 * sums[a:b, 0]
     parent = list(range(n))
     for k in range(len(slabs) - 1):
@@ -90,6 +132,8 @@ def merge_slabs(slabs: list[SlabResult], width: int, height: int) -> np.ndarray:
             for f in ("peak_intensity", "peak_x", "peak_y", "peak_z"):
                 a[f] = b[f]
         sums[r] += sums[i]
+        if absm is not None:
+            absm[r] += absm[i]
     # Reflection3D::center_of_mass / peak_centroid_distance, recomputed from the exact sums for
     # every surviving spot: merged ones changed, and slab-local z became sweep z for the rest
     for r in np.flatnonzero(roots == np.arange(n)):
@@ -104,7 +148,13 @@ def merge_slabs(slabs: list[SlabResult], width: int, height: int) -> np.ndarray:
         s["peak_centroid_distance"] = np.sqrt(np.float32(np.float32(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]))
     keep = roots == np.arange(n)
     out = spots[keep]
-    return out[np.argsort(out["label"], kind="stable")]
+    order = np.argsort(out["label"], kind="stable")
+    if not with_sums:
+        return out[order]
+    out = out[order]
+    sums_out = sums[keep][order]
+    mom_out = _relative_moments(out, sums_out, absm[keep][order]) if absm is not None else None
+    return out, sums_out.astype(np.uint64), mom_out
 
 
 def gather_and_merge(local: SlabResult, width: int, height: int, group=None) -> np.ndarray:
@@ -121,4 +171,4 @@ def slab_result_from(sf, z0: int, n_frames: int) -> SlabResult:
     """Finish the sweep recorded in Spotfinder `sf` and package it for merging."""
     spots = sf.sweep_finish()
     return SlabResult(z0, n_frames, spots, sf.sweep_export_sums(), sf.sweep_export_plane(0),
-                      sf.sweep_export_plane(1))
+                      sf.sweep_export_plane(1), sf.sweep_export_moments())

@@ -221,6 +221,36 @@ int ffs_sweep_export_plane(ffs_ctx *ctx, int which, uint32_t **index_and_compone
  * 4 values per spot: sum I, sum (2x+1) I, sum (2y+1) I, sum (2z+1) I (z local to the slab).
  * These are what slab merging needs; centroids alone cannot be merged. */
 int ffs_sweep_export_sums(ffs_ctx *ctx, uint64_t **sums, size_t *n_spots);
+
+/* ---- per-spot variances in Kabsch space (Reflection3D::variances_in_kabsch_space,
+ *      connected_components.cc:159-203; caller loop spotfinder.cc:1152-1216) ----------------
+ * Second moments of each 3D component of the last ffs_sweep_finish, same order, 4 per spot,
+ * taken relative to the spot's own bounding-box minimum (x_min, y_min, z_min) so that they
+ * stay small and exact:  sum I u^2, sum I v^2, sum I u v, sum I w^2   with
+ * u = x - x_min, v = y - y_min, w = z - z_min.  Together with ffs_sweep_export_sums they are
+ * everything the variances need; like the sums they can be merged across slabs. */
+int ffs_sweep_export_moments(ffs_ctx *ctx, uint64_t **moments, size_t *n_spots);
+
+/* The experiment description the reference builds at spotfinder.cc:1157-1168: a dx2 Panel
+ * from distance / beam centre / pixel size with fast = +x, slow = -y (dx2 detector.cxx:243-268,
+ * no parallax correction: thickness = mu = 0), s0 = (0, 0, -1/wavelength), rotation axis +x,
+ * oscillation in degrees. */
+typedef struct ffs_kabsch_geometry {
+    double distance_mm;
+    double beam_center_x_px, beam_center_y_px;
+    double pixel_size_x_mm, pixel_size_y_mm;
+    double wavelength;
+    double oscillation_width_deg;
+} ffs_kabsch_geometry;
+
+/* For every spot: sigma_b_variance = (var_e1 + var_e2) / 2, sigma_m_variance = var_e3,
+ * bbox_depth = z_max - z_min + 1 (the tuple variances_in_kabsch_space returns), evaluated on
+ * the device from {spots, sums, moments} (host arrays of n, 4n and 4n entries; any output
+ * pointer may be NULL).  s1 and phi are taken at the spot's centre of mass as the caller
+ * loop does.  Spots with zero total intensity give NaN, as the reference's 0/0 does. */
+int ffs_kabsch_variances(ffs_ctx *ctx, const ffs_kabsch_geometry *geometry, const ffs_spot *spots,
+                         const uint64_t *sums, const uint64_t *moments, size_t n,
+                         double *sigma_b_variance, double *sigma_m_variance, int32_t *bbox_depth);
 void ffs_free(void *p);
 
 /* filter_reflections (connected_components.cc:207-236): stable, in place; returns kept. */

@@ -227,3 +227,70 @@ def process_frame(image, mask, params=None, algorithm=ALGO_DISPERSION, min_spot_
         raise ValueError(f"process_frame failed: {rc}")
     return dict(num_strong_pixels=counts[0], n_spots_total=counts[1], num_strong_pixels_filtered=counts[2],
                 n_spots_filtered=counts[3])
+
+
+def kabsch_variances(labels, image, spots, geometry):
+    """Reflection3D::variances_in_kabsch_space (connected_components.cc:159-203) driven as the
+    caller loop does (spotfinder.cc:1157-1196), restated pixel by pixel in fp64 -- PARITY
+    UNPINNED: the reference's own check (tests/test_spotfinder.py:108-114) needs a dataset that
+    is not in the tree, and dx2 / Eigen are not available to compile the original here.
+
+    labels/image: (Z, H, W) from connected_components(); spots: its records (com_* as float32,
+    the reference's center_of_mass() type).  geometry: dict with the ffs_kabsch_geometry keys.
+    Returns (sigma_b_variance, sigma_m_variance, bbox_depth) arrays, one entry per spot.
+    Geometry: dx2 Panel(distance, beam_center, pixel_size) with fast=+x, slow=-y
+    (dx2/dx2/detector.cxx:243-268), px_to_mm without parallax (:193-198), get_lab_coord = d * (x, y, 1)
+    (:211-213); s0 = (0, 0, -1/wavelength); rotation axis m2 = +x; Scan image range starts at 1."""
+    g = geometry
+    psx, psy = float(g["pixel_size_x_mm"]), float(g["pixel_size_y_mm"])
+    fast = np.array([1.0, 0.0, 0.0])
+    slow = np.array([0.0, -1.0, 0.0])
+    origin = np.array([0.0, 0.0, -1.0 * float(g["distance_mm"])])
+    origin = origin - float(g["beam_center_x_px"]) * psx * fast
+    origin = origin - float(g["beam_center_y_px"]) * psy * slow
+    s0 = np.array([0.0, 0.0, -1.0 / float(g["wavelength"])])
+    m2 = np.array([1.0, 0.0, 0.0])
+    osc_start, osc_width = 0.0, float(g["oscillation_width_deg"])
+    image_range_0 = 1
+    deg_to_rad = np.pi / 180.0
+
+    def lab(xmm, ymm):
+        return fast * xmm + slow * ymm + origin
+
+    zz, yy, xx = np.nonzero(labels >= 0) if labels.dtype.kind == "i" else np.nonzero(labels)
+    lab_of = labels[zz, yy, xx]
+    order = np.argsort(lab_of, kind="stable")
+    zz, yy, xx, lab_of = zz[order], yy[order], xx[order], lab_of[order]
+    inten = image[zz, yy, xx].astype(np.float64)
+    starts = np.searchsorted(lab_of, spots["label"].astype(lab_of.dtype), side="left")
+    ends = np.searchsorted(lab_of, spots["label"].astype(lab_of.dtype), side="right")
+    n = len(spots)
+    sb, sm, depth = np.zeros(n), np.zeros(n), np.zeros(n, np.int32)
+    for i, s in enumerate(spots):
+        cx, cy, cz = float(s["com_x"]), float(s["com_y"]), float(s["com_z"])
+        s1 = lab(cx * psx, cy * psy)
+        phi = (osc_start + (cz - image_range_0) * osc_width) * deg_to_rad
+        e1 = np.cross(s1, s0)
+        e1 = e1 / np.sqrt(e1.dot(e1))
+        e2 = np.cross(s1, e1)
+        e2 = e2 / np.sqrt(e2.dot(e2))
+        mags1 = np.sqrt(s1.dot(s1))
+        zeta = m2.dot(e1)
+        varx = vary = varz = tot = 0.0
+        for k in range(starts[i], ends[i]):
+            x, y, z = xx[k] + 0.5, yy[k] + 0.5, zz[k] + 0.5
+            delta = lab(x * psx, y * psy) - s1
+            eps1 = e1.dot(delta) / mags1
+            eps2 = e2.dot(delta) / mags1
+            phi_dash = (osc_start + (z - image_range_0) * osc_width) * deg_to_rad
+            eps3 = (phi_dash - phi) * zeta
+            varx += inten[k] * eps1 * eps1
+            vary += inten[k] * eps2 * eps2
+            varz += inten[k] * eps3 * eps3
+            tot += inten[k]
+        with np.errstate(invalid="ignore", divide="ignore"):
+            varx, vary, varz = np.float64(varx) / tot, np.float64(vary) / tot, np.float64(varz) / tot
+        sb[i] = (varx + vary) / 2.0
+        sm[i] = varz
+        depth[i] = int(s["z_max"]) - int(s["z_min"]) + 1
+    return sb, sm, depth

@@ -101,9 +101,23 @@ def test_rotation_sweep_3d_and_start_index(tmp_path):
     assert rc == 0 and err == ""
     assert sorted(l["file-number"] for l in lines) == list(range(6))  # 0-based loop counter (N16)
     strong = np.stack([oracle.dispersion(f, mask) for f in sweep[2:]])
-    _, spots = oracle.connected_components(strong, sweep[2:], want_labels=False)
+    labels, spots = oracle.connected_components(strong, sweep[2:])
     kept, rs, rp = oracle.filter_spots(spots, 3, 2.0)
     assert int(re.search(r"Calculated\s+(\d+)\s+spots", out).group(1)) == len(spots)
+    # estimated sigma_b / sigma_m over the kept reflections (spotfinder.cc:1180-1212)
+    h, w = mask.shape
+    geom = dict(distance_mm=150.0, beam_center_x_px=w / 2, beam_center_y_px=h / 2, pixel_size_x_mm=0.075,
+                pixel_size_y_mm=0.075, wavelength=0.976, oscillation_width_deg=0.1)
+    sb, sm, depth = oracle.kabsch_variances(labels, sweep[2:], kept, geom)
+    got_b = float(re.search(r"Estimated sigma_b \(degrees\): ([0-9.]+)", out).group(1))
+    assert got_b == pytest.approx(np.sqrt(sb.mean()) * 180 / np.pi, rel=1e-4, abs=2e-6)
+    deep = depth >= 5
+    m = re.search(r"Estimated sigma_m \(degrees\): ([0-9.]+), calculated on (\d+) spots", out)
+    if deep.any():
+        assert int(m.group(2)) == int(deep.sum())
+        assert float(m.group(1)) == pytest.approx(np.sqrt(sm[deep].mean()) * 180 / np.pi, rel=1e-4, abs=2e-6)
+    else:
+        assert m is None
     if rs:
         assert int(re.search(r"Filtered\s+(\d+)\s+spots with size < 3 pixels", out).group(1)) == rs
     if rp:

@@ -37,13 +37,18 @@ def oracle_slab(strong, sweep, z0, z1) -> SlabResult:
     sums = np.zeros((len(spots), 4), dtype=object)
     for c, i, x, y, z in zip(comp, inten, xx, yy, zz):
         sums[c] += np.array([i, (2 * int(x) + 1) * i, (2 * int(y) + 1) * i, (2 * int(z) + 1) * i], dtype=object)
+    moments = np.zeros((len(spots), 4), dtype=object)
+    for c, i, x, y, z in zip(comp, inten, xx, yy, zz):
+        u, v, q = int(x) - int(out["x_min"][c]), int(y) - int(out["y_min"][c]), int(z) - int(out["z_min"][c])
+        moments[c] += np.array([i * u * u, i * v * v, i * u * v, i * q * q], dtype=object)
     w = s.shape[2]
 
     def plane(zl):
         sel = zz == zl
         return np.stack([(yy[sel] * w + xx[sel]).astype(np.uint32), comp[sel].astype(np.uint32)], axis=1)
 
-    return SlabResult(z0, z1 - z0, out, sums.astype(np.uint64), plane(0), plane(z1 - z0 - 1))
+    return SlabResult(z0, z1 - z0, out, sums.astype(np.uint64), plane(0), plane(z1 - z0 - 1),
+                      moments.astype(np.uint64))
 
 
 def check(got, want):
@@ -62,6 +67,41 @@ def test_merge_matches_whole_sweep(world):
     if world > 1:  # slab cuts really split components
         assert sum(len(s.spots) for s in slabs) > len(want)
     check(merge_slabs(slabs, g.width, g.height), want)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_merged_sums_and_moments_are_exact(world):
+    """Second moments (the inputs of the Kabsch-space variances) survive slab merging exactly."""
+    g, sweep, strong = make_sweep(nz=9)
+    whole = oracle_slab(strong, sweep, 0, len(sweep))
+    slabs = [oracle_slab(strong, sweep, *slab_bounds(len(sweep), world, r)) for r in range(world)]
+    spots, sums, moments = merge_slabs(slabs, g.width, g.height, with_sums=True)
+    check(spots, whole.spots)
+    assert np.array_equal(sums, whole.sums)
+    assert np.array_equal(moments, whole.moments)
+
+
+def test_oracle_kabsch_variances_known_answers():
+    """Hand-checkable cases of the per-pixel restatement: a one-pixel spot has zero variance;
+    two equal pixels one frame apart have var_e3 = (half a frame of rotation * zeta)^2."""
+    strong = np.zeros((3, 40, 50), np.uint8)
+    image = np.zeros((3, 40, 50), np.uint16)
+    strong[0, 5, 7] = 1
+    image[0, 5, 7] = 9
+    strong[1:3, 30, 20] = 1
+    image[1:3, 30, 20] = 100
+    labels, spots = oracle.connected_components(strong, image)
+    geom = dict(distance_mm=150.0, beam_center_x_px=25.0, beam_center_y_px=20.0, pixel_size_x_mm=0.075,
+                pixel_size_y_mm=0.075, wavelength=1.0, oscillation_width_deg=0.1)
+    sb, sm, depth = oracle.kabsch_variances(labels, image, spots, geom)
+    assert list(depth) == [1, 2]
+    assert sb[0] == 0.0 and sm[0] == 0.0
+    assert abs(sb[1]) < 1e-30
+    # zeta = e1.x with e1 = normalise(s1 x s0), s1 = lab coordinate of the centre of mass
+    s1 = np.array([(20.5 - 25.0) * 0.075, -(30.5 - 20.0) * 0.075, -150.0])
+    e1 = np.cross(s1, np.array([0, 0, -1.0]))
+    zeta = (e1 / np.linalg.norm(e1))[0]
+    np.testing.assert_allclose(sm[1], (0.5 * 0.1 * np.pi / 180.0 * zeta) ** 2, rtol=1e-12)
 
 
 def test_component_spanning_three_slabs_and_empty_boundary():
