@@ -194,10 +194,52 @@ extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, s
         }
     }
     if (rc == FFS_OK && c->sweep_on) rc = sweep_record(c, slot, s.frame_id, cnt[CNT_STRONG]);
+    if (rc == FFS_OK && c->keep_pixels) {  // --writeout: the frame's strong-pixel list, before the slot is reused
+        c->last_pixels.resize(cnt[CNT_STRONG]);
+        if (cnt[CNT_STRONG]) {
+            cudaError_t e = cudaMemcpy(c->last_pixels.data(), c->d_px_index + (size_t)slot * c->cap_strong,
+                                       cnt[CNT_STRONG] * 4ull, cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) {
+                c->err = cudaGetErrorString(e);
+                rc = FFS_ERR_CUDA;
+            }
+        }
+    }
+    if (rc == FFS_OK && c->keep_pixels && c->keep_frame) {  // the dense frame as the device saw it
+        const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
+        c->last_frame.resize(row * c->p.height);
+        cudaError_t e = cudaMemcpy2D(c->last_frame.data(), row, c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
+                                     row, c->p.height, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            c->err = cudaGetErrorString(e);
+            rc = FFS_ERR_CUDA;
+        }
+    }
     {
         std::lock_guard<std::mutex> lk(c->mu);
         s.state = 0;
     }
     c->cv.notify_all();
     return rc;
+}
+
+extern "C" int ffs_keep_pixel_lists(ffs_ctx* c, int on) {
+    if (!c) return FFS_ERR_ARG;
+    c->keep_pixels = on != 0;
+    c->keep_frame = on == 2;
+    return FFS_OK;
+}
+
+extern "C" int ffs_last_frame(ffs_ctx* c, const void** pixels, size_t* bytes) {
+    if (!c || !pixels || !c->keep_frame) return FFS_ERR_ARG;
+    *pixels = c->last_frame.data();
+    if (bytes) *bytes = c->last_frame.size();
+    return FFS_OK;
+}
+
+extern "C" int ffs_last_pixel_list(ffs_ctx* c, const uint32_t** index, size_t* n) {
+    if (!c || !index || !n || !c->keep_pixels) return FFS_ERR_ARG;
+    *index = c->last_pixels.data();
+    *n = c->last_pixels.size();
+    return FFS_OK;
 }

@@ -14,6 +14,7 @@
 #include "../../../include/ffs_b200.h"
 #include "args.hpp"
 #include "bslz4.hpp"
+#include "png_writer.hpp"
 #include "reader.hpp"
 
 #ifndef FFS_VERSION

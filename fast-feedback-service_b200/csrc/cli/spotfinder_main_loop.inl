@@ -16,6 +16,17 @@
         return 1;
     }
     printf("Mask has %llu valid pixels of %u\n", (unsigned long long)ffs_mask_valid_count(ctx), width * height);
+    // --writeout (spotfinder.cc:626-646,653-679): white = valid, red = masked
+    auto write_mask_png = [&](const char* name, const uint8_t* m) {
+        std::vector<uint8_t> rgb((size_t)width * height * 3, 255);
+        for (size_t k = 0; k < (size_t)width * height; ++k)
+            if (!m[k]) rgb[3 * k + 1] = rgb[3 * k + 2] = 0;
+        if (!pngw::write_rgb(name, rgb.data(), width, height)) printf("Warning: could not write %s\n", name);
+    };
+    if (args.writeout) {
+        write_mask_png("mask_source.png", reader.get_mask().data());
+        ffs_keep_pixel_lists(ctx, 2);
+    }
     if (args.dmin > 0 || args.dmax > 0) {  // apply_resolution_filtering, spotfinder.cc:110-137,650-652
         if (ffs_apply_resolution_mask(ctx, wavelength, det.distance, det.beam_center_x, det.beam_center_y,
                                       det.pixel_size_x, det.pixel_size_y, args.dmin, args.dmax)) {
@@ -23,6 +34,10 @@
             return 1;
         }
         printf("Resolution mask applied: %llu valid pixels remain\n", (unsigned long long)ffs_mask_valid_count(ctx));
+        if (args.writeout) {
+            std::vector<uint8_t> calc((size_t)width * height);
+            if (ffs_get_mask(ctx, calc.data()) == FFS_OK) write_mask_png("mask_calculated.png", calc.data());
+        }
     }
     if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain\n");
     if (args.save_h5) printf("Note: results_ffs.h5 cannot be written by this build (libhdf5 unavailable)\n");
@@ -151,6 +166,49 @@
                                  ",\"num_strong_pixels\":" + std::to_string(r.num_strong_pixels);
                 if (args.output_for_index) js += ",\"spot_centers\":[" + centers + "]";
                 pipe->send(js + "}");
+            }
+            if (args.writeout) {  // image_NNNNN.png + pixels_NNNNN.txt (spotfinder.cc:939-994)
+                const uint32_t* pidx = nullptr;
+                size_t np = 0;
+                const void* fr = nullptr;
+                if (ffs_last_pixel_list(ctx, &pidx, &np) == FFS_OK && ffs_last_frame(ctx, &fr, nullptr) == FFS_OK) {
+                    const pixel_t* img = static_cast<const pixel_t*>(fr);
+                    std::vector<uint8_t> rgb(px * 3);
+                    for (size_t k = 0; k < px; ++k) {
+                        const uint8_t gray = (uint8_t)std::max(0.0f, 255.99f - static_cast<float>(img[k]) * 10);
+                        rgb[3 * k] = rgb[3 * k + 1] = rgb[3 * k + 2] = gray;
+                    }
+                    auto blue = [&](long x, long y) {  // (the reference does not clip the frame: we do)
+                        if (x < 0 || y < 0 || x >= (long)width || y >= (long)height) return;
+                        uint8_t* q = &rgb[3 * ((size_t)y * width + x)];
+                        q[0] = 0; q[1] = 0; q[2] = 255;
+                    };
+                    for (size_t i = 0; i < n; ++i) {  // get_boxes(): components of at least min_spot_size pixels
+                        const ffs_spot& b = spots[i];
+                        if (args.min_spot_size > 0 && b.num_pixels < args.min_spot_size) continue;
+                        for (long edge = 5; edge <= 7; ++edge) {
+                            for (long x = (long)b.x_min - edge; x <= (long)b.x_max + edge; ++x) {
+                                blue(x, (long)b.y_min - edge);
+                                blue(x, (long)b.y_max + edge);
+                            }
+                            for (long y = (long)b.y_min - edge; y <= (long)b.y_max + edge; ++y) {
+                                blue((long)b.x_min - edge, y);
+                                blue((long)b.x_max + edge, y);
+                            }
+                        }
+                    }
+                    char name[64];
+                    snprintf(name, sizeof name, "pixels_%05u.txt", image_num);
+                    FILE* pf = fopen(name, "w");
+                    for (size_t i = 0; i < np; ++i) {
+                        uint8_t* q = &rgb[3 * (size_t)pidx[i]];
+                        q[0] = 255; q[1] = 0; q[2] = 0;
+                        if (pf) fprintf(pf, "%4d, %4d\n", (int)(pidx[i] % width), (int)(pidx[i] / width));
+                    }
+                    if (pf) fclose(pf);
+                    snprintf(name, sizeof name, "image_%05u.png", image_num);
+                    if (!pngw::write_rgb(name, rgb.data(), width, height)) printf("Warning: could not write %s\n", name);
+                }
             }
             printf("Thread %2d finished image %4u with %5u strong pixels, %4u filtered reflections (%u pixels)\n",
                    thread_of[image_num], image_num, r.num_strong_pixels, r.n_spots_total, r.num_strong_pixels_filtered);

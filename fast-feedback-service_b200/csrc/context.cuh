@@ -126,6 +126,10 @@ struct ffs_ctx {
     std::vector<std::vector<uint32_t>> sweep_index;  // per frame strong-pixel linear indices
     std::vector<std::vector<uint32_t>> sweep_value;
     std::vector<uint64_t> sweep_sums;      // per 3D component: exact sum I, (2x+1)I, (2y+1)I, (2z+1)I
+    bool keep_pixels = false;              // ffs_keep_pixel_lists
+    bool keep_frame = false;
+    std::vector<uint8_t> last_frame;       // dense pixels of the last ffs_wait frame (keep mode 2)
+    std::vector<uint32_t> last_pixels;     // strong-pixel linear indices of the last ffs_wait frame
     std::vector<uint64_t> sweep_moments;   // per 3D component: bbox-relative sum I u^2, I v^2, I u v, I w^2
     std::vector<uint32_t> sweep_plane[2];  // {index, component rank} of the first / last slice
 };

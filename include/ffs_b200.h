@@ -198,6 +198,15 @@ int ffs_slot_buffers(ffs_ctx *ctx, int slot, void **pinned_pixels, void **pinned
 int ffs_decode_chunk_device(ffs_ctx *ctx, int slot, const void *chunk, size_t chunk_bytes,
                             void *frame_out);
 
+/* Diagnostics (--writeout, spotfinder.cc:939-994 writes pixels_NNNNN.txt and image_NNNNN.png from
+ * the strong-pixel mask it copied back): when switched on, ffs_wait also keeps the frame's
+ * strong-pixel list (ascending linear indices y*width + x); *index stays valid until the next
+ * ffs_wait on this context.  on = 2 also keeps the dense frame as the device saw it (after the
+ * device decode, if any), for the diagnostic picture. */
+int ffs_keep_pixel_lists(ffs_ctx *ctx, int on);
+int ffs_last_pixel_list(ffs_ctx *ctx, const uint32_t **index, size_t *n);
+int ffs_last_frame(ffs_ctx *ctx, const void **pixels, size_t *bytes);
+
 /* ---- rotation sweeps: 3D connected components (find_3d_components) ---------------------- */
 /* Frames processed with sweep recording on keep their strong-pixel lists on the device;
  * ffs_sweep_finish labels the whole stack (6-connectivity: index+1, index+width, same

@@ -34,11 +34,11 @@ def write_stream(d: Path, frames, mask, bits, omega_increment=None, start=0):
         (d / f"image_{start + i:06d}_2").write_bytes(compress_chunk(f))
 
 
-def run(exe, args, timeout=120, host_decode=False):
+def run(exe, args, timeout=120, host_decode=False, cwd=None):
     r, w = os.pipe()
     env = dict(os.environ, FFS_HOST_DECODE="1" if host_decode else "0")
     proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=subprocess.PIPE,
-                            stderr=subprocess.PIPE, env=env)
+                            stderr=subprocess.PIPE, env=env, cwd=cwd)
     os.close(w)
     lines = []
     with os.fdopen(r) as f:
@@ -96,8 +96,10 @@ def test_rotation_sweep_3d_and_start_index(tmp_path):
     mask = synth.make_mask(g)
     sweep = synth.make_sweep(g, mask, 8, np.uint16, n_reflections=40)
     write_stream(tmp_path, sweep, mask, 16, omega_increment=0.1)
+    outdir = tmp_path / "out"
+    outdir.mkdir()
     rc, lines, out, err = run("spotfinder", [str(tmp_path), "--threads", "2", "--writeout", "--start-index", "2",
-                                              "--images", "6"])
+                                              "--images", "6"], cwd=outdir)
     assert rc == 0 and err == ""
     assert sorted(l["file-number"] for l in lines) == list(range(6))  # 0-based loop counter (N16)
     strong = np.stack([oracle.dispersion(f, mask) for f in sweep[2:]])
@@ -123,6 +125,57 @@ def test_rotation_sweep_3d_and_start_index(tmp_path):
     if rp:
         assert int(re.search(r"Filtered\s+(\d+)\s+spots with peak-centroid distance > 2", out).group(1)) == rp
     assert int(re.search(r"Found (\d+) spots", out).group(1)) == len(kept)
+
+
+def read_png_rgb(path):
+    """Decode the stored-deflate RGB8 PNGs the executable writes (zlib inflates them like any other)."""
+    import zlib
+    b = path.read_bytes()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(b):
+        n, typ = struct.unpack(">I4s", b[pos:pos + 8])
+        data = b[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", b[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + data)
+        if typ == b"IHDR":
+            w, h, depth, colour = struct.unpack(">IIBB", data[:10])
+            assert (depth, colour) == (8, 2)
+        elif typ == b"IDAT":
+            idat += data
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    assert not raw[:, 0].any()  # filter type 0 on every row
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+def test_writeout_files(tmp_path):
+    """--writeout: mask_source.png, mask_calculated.png, image_NNNNN.png, pixels_NNNNN.txt
+    (spotfinder.cc:626-679,939-994)."""
+    g = synth.small_geometry(200, 160)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 2, np.uint16, config=6, n_spots=12)
+    write_stream(tmp_path, frames, mask, 16)
+    outdir = tmp_path / "out"
+    outdir.mkdir()
+    rc, lines, out, err = run("spotfinder", [str(tmp_path), "--threads", "1", "--writeout", "--dmin", "30"], cwd=outdir)
+    assert rc == 0 and err == ""
+    src = read_png_rgb(outdir / "mask_source.png")
+    assert np.array_equal(src[..., 1] == 255, mask != 0) and (src[..., 0] == 255).all()
+    calc = read_png_rgb(outdir / "mask_calculated.png")
+    valid = calc[..., 1] == 255
+    assert valid.sum() < (mask != 0).sum() and not (valid & (mask == 0)).any()  # resolution filter only removes
+    for i, f in enumerate(frames):
+        strong = oracle.dispersion(f, valid.astype(np.uint8))
+        yy, xx = np.nonzero(strong)
+        want_txt = "".join(f"{x:4d}, {y:4d}\n" for x, y in zip(xx, yy))
+        assert (outdir / f"pixels_{i:05d}.txt").read_text() == want_txt
+        img = read_png_rgb(outdir / f"image_{i:05d}.png")
+        red = (img[..., 0] == 255) & (img[..., 1] == 0) & (img[..., 2] == 0)
+        assert np.array_equal(red, strong != 0)
+        # a pixel away from spots and boxes keeps the reference's grey ramp: max(0, 255.99 - 10 v)
+        plain = ~red & ~((img[..., 2] == 255) & (img[..., 0] == 0))
+        want_grey = np.maximum(0.0, np.float32(255.99) - f.astype(np.float32) * 10).astype(np.uint8)
+        assert np.array_equal(img[..., 0][plain], want_grey[plain])
 
 
 def test_list_devices_and_bad_args():
