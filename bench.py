@@ -211,7 +211,7 @@ def ncu_traffic_per_frame():
     """dram bytes (read+write) per frame of the prefilter kernel from the committed ncu capture."""
     p = ROOT / "profiles" / "roofline_traffic.json"
     try:
-        return float(json.loads(p.read_text())["prefilter_dram_bytes_per_frame"])
+        return float(json.loads(p.read_text())["fused_dram_bytes_per_frame"])
     except Exception:
         return None
 

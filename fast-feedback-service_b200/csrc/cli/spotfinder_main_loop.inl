@@ -39,7 +39,7 @@
             if (ffs_get_mask(ctx, calc.data()) == FFS_OK) write_mask_png("mask_calculated.png", calc.data());
         }
     }
-    if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain\n");
+    if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain; use tests/validate_stream.py\n");
     if (args.save_h5) printf("Note: results_ffs.h5 cannot be written by this build (libhdf5 unavailable)\n");
     std::unique_ptr<PipeHandler> pipe;
     if (args.pipe_fd != -1) pipe = std::make_unique<PipeHandler>(args.pipe_fd);

@@ -178,6 +178,21 @@ def test_writeout_files(tmp_path):
         assert np.array_equal(img[..., 0][plain], want_grey[plain])
 
 
+def test_validate_stream_script(tmp_path):
+    """tests/validate_stream.py: the field parity check that stands in for --validate."""
+    import sys
+    g = synth.small_geometry(180, 140)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 3, np.uint16, config=6, n_spots=10)
+    write_stream(tmp_path, frames, mask, 16)
+    script = Path(__file__).resolve().parent / "validate_stream.py"
+    for algo in ("dispersion", "dispersion_extended"):
+        r = subprocess.run([sys.executable, str(script), str(tmp_path), "--algorithm", algo], capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert r.stdout.count("identical") == 3 and "validation passed" in r.stdout
+
+
 def test_list_devices_and_bad_args():
     out = subprocess.run([str(BIN / "spotfinder"), "--list-devices"], capture_output=True, text=True)
     assert out.returncode == 0 and re.search(r"0: .+ \(CUDA \d+\.\d+\)", out.stdout)  # service.py:220-238 probes this
