@@ -66,13 +66,19 @@ static int cc_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     fill_cc_args(c, a, first_slot, n);
     const dim3 gchunks((unsigned)a.n_chunks, (unsigned)n);
     const dim3 gpix((unsigned)std::max(1, c->sm_count / std::max(1, std::min(n, 8))), (unsigned)n);
-    cc_count_kernel<<<gchunks, 256, 0, st>>>(a);
+    // chunk_count was filled by the threshold kernels as they set the strong bits (set_strong);
+    // cc_count_kernel is kept for planes that come from elsewhere
+    static const int recount = env_int("FFS_CC_RECOUNT", 0);
+    if (recount) {
+        cc_count_kernel<<<gchunks, 256, 0, st>>>(a);
+        c->launches++;
+    }
     cc_scan_kernel<<<(unsigned)n, 256, 0, st>>>(a);
     cc_extract_kernel<<<gchunks, 256, 0, st>>>(a);
     cc_link_kernel<<<gpix, 256, 0, st>>>(a);
     cc_reduce_kernel<<<gpix, 256, 0, st>>>(a);
     cc_finalize_kernel<<<(unsigned)n, kFinalizeThreads, 0, st>>>(a);
-    c->launches += 6;
+    c->launches += 5;
     FFS_CK(c, cudaGetLastError());
     return FFS_OK;
 }

@@ -320,6 +320,8 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.thr_floor = (int)std::min(std::floor(c->p.threshold), 1073741824.0);
     a.mcount = c->d_mcount;
     a.m_pitch = c->m_pitch;
+    a.chunk_count = c->d_chunk_count;  // zeroed by threshold_impl; consumed by cc_scan_kernel
+    a.n_chunks = c->n_chunks;
 }
 
 template <typename PixelT, int PPL>
@@ -448,6 +450,8 @@ static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
                               c->bits_stride * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_strong_count + first_slot, 0, sizeof(unsigned) * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_cand_count + first_slot, 0, sizeof(unsigned) * n, st));
+    FFS_CK(c, cudaMemsetAsync(c->d_chunk_count + (size_t)first_slot * c->n_chunks, 0,
+                              sizeof(uint32_t) * c->n_chunks * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
     static const int two_kernel = env_int("FFS_TWO_KERNEL", 0);  // A/B: the round-1 prefilter + resolve pair
     if (two_kernel || env_int("FFS_FORCE_BRUTE", 0)) {

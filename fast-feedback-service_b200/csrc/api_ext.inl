@@ -11,6 +11,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     fill_thresh_args(c, a, first_slot, n);
     a.strong_bits = reinterpret_cast<uint32_t*>(c->d_ext1);
     a.strong_count = c->d_ext_count;
+    a.chunk_count = nullptr;  // the D plane is not the connected-components input
     static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
     if (brute) {
         a.force_brute = 1;

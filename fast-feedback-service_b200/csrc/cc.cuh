@@ -39,6 +39,7 @@ enum { CNT_STRONG = 0, CNT_STRONG_RAW, CNT_COMPONENTS, CNT_SPOTS_TOTAL, CNT_STRO
        CNT_SPOTS_FILTERED, CNT_STATUS, CNT_PAD, CNT_N };
 
 constexpr int kChunkWords = 1024;  // strong-plane words per compaction block
+static_assert(kChunkWords == 1 << 10, "set_strong (threshold.cuh) derives the chunk with a shift by 10");
 
 struct CCArgs {
     int width, height, n_frames, slot0;

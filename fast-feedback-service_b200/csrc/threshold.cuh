@@ -58,6 +58,8 @@ struct ThreshArgs {
     float prefilter_k;  // nsig_s^2 * (1 - 1e-4): conservative
     float sig_k;        // nsig_s * (1 - 1e-4)            (fused kernel)
     int thr_floor;      // floor(threshold): v > threshold <=> v > thr_floor for integer v
+    uint32_t* chunk_count;  // per slot: strong pixels per 1024-word chunk of the strong plane (the
+    int n_chunks;           // connected-components compaction's first pass); NULL = do not count
     const uint8_t* mcount;  // per pixel: mask-valid pixels in its image-clipped 7x7 window
     size_t m_pitch;         // (group_info_kernel); 49 <=> window inside the image and fully valid
 };
@@ -299,11 +301,14 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
 }
 
 __device__ __forceinline__ void set_strong(const ThreshArgs& a, int z, int col, int row) {
+    const size_t word = (size_t)row * (a.strong_pitch >> 2) + (col >> 5);
     uint32_t* w = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(a.strong_bits) +
-                                              (size_t)z * a.strong_frame_stride +
-                                              (size_t)row * a.strong_pitch) +
-                  (col >> 5);
-    atomicOr(w, 1u << (col & 31));
+                                              (size_t)z * a.strong_frame_stride) + word;
+    const uint32_t bit = 1u << (col & 31);
+    const uint32_t before = atomicOr(w, bit);
+    // strong pixels are sparse, so counting them per compaction chunk here (one more atomic
+    // per strong pixel) replaces a kernel that re-reads every strong plane (cc_count_kernel)
+    if (a.chunk_count && !(before & bit)) atomicAdd(a.chunk_count + (size_t)z * a.n_chunks + (word >> 10), 1u);
 }
 
 // grid: (blocks, n_frames).  One thread per candidate of frame blockIdx.y (grid-stride).

@@ -52,6 +52,21 @@ def test_dispersion_random_mask_and_extremes(dtype):
     assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
 
 
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+@pytest.mark.parametrize("lam", [9000.0, 9362.0, 30000.0])
+@pytest.mark.parametrize("mask_kind", ["random", "modules"])
+def test_dispersion_background_at_and_above_the_clamp(lam, mask_kind, dtype):
+    """The streaming kernel's pruning bound is built from values clamped to 9362; a background
+    at or above the clamp leaves (almost) nothing to prune.  Results must not change."""
+    img, mask = random_frame(96, 300, dtype, seed=int(lam), lam=lam, n_spots=6, mask_kind=mask_kind)
+    img[10:20, 30:60] = 9361
+    img[30:40, 30:60] = 9362
+    img[50:60, 30:60] = 9363
+    want = oracle.dispersion(img, mask)
+    got = run_gpu(img, mask)
+    assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
+
+
 def test_dispersion_all_zero_all_masked_no_mask():
     h, w = 60, 300
     z = np.zeros((h, w), np.uint16)
