@@ -119,7 +119,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     cc3_init_kernel<<<grid, 256, 0, c->stream>>>(a);
     cc3_link_kernel<<<grid, 256, 0, c->stream>>>(a);
     cc3_reduce_kernel<<<grid, 256, 0, c->stream>>>(a);
-    cc3_finalize_kernel<<<1, 256, 0, c->stream>>>(a);
+    cc3_finalize_kernel<<<1, kFinalizeThreads, 0, c->stream>>>(a);
     cc3_moments_kernel<<<grid, 256, 0, c->stream>>>(a);
     c->launches += 5;
     SWEEP_CK(cudaGetLastError());

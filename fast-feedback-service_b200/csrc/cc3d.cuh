@@ -73,18 +73,30 @@ __global__ void __launch_bounds__(256) cc3_reduce_kernel(const CC3Args a) {
     }
 }
 
-// one block: ordered compaction of roots -> spots
-__global__ void __launch_bounds__(256) cc3_finalize_kernel(const CC3Args a) {
+// one block of 1024 threads: ordered compaction of roots -> spots (ranks as in cc_finalize_kernel:
+// ballot + popc inside a warp, one pass over the 32 warp totals, one barrier per 1024 entries)
+__global__ void __launch_bounds__(kFinalizeThreads) cc3_finalize_kernel(const CC3Args a) {
     const uint32_t W = (uint32_t)a.width;
     const uint64_t px = (uint64_t)a.width * a.height;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ uint32_t warp_roots[2][32];
     uint32_t running = 0;
-    for (uint32_t base = 0; base < a.total; base += 256) {
+    int buf = 0;
+    for (uint32_t base = 0; base < a.total; base += kFinalizeThreads, buf ^= 1) {
         const uint32_t i = base + threadIdx.x;
         const bool is_root = i < a.total && a.parent[i] == i;
-        uint32_t tot;
-        const uint32_t rank = running + block_exclusive_scan_256(is_root ? 1u : 0u, &tot);
-        running += tot;
+        const unsigned ball = __ballot_sync(0xffffffffu, is_root);
+        if (lane == 0) warp_roots[buf][warp] = __popc(ball);
+        __syncthreads();
+        const uint32_t wr = warp_roots[buf][lane];
+        uint32_t before = lane < warp ? wr : 0u, all = wr;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            before += __shfl_xor_sync(0xffffffffu, before, off);
+            all += __shfl_xor_sync(0xffffffffu, all, off);
+        }
         if (is_root) {
+            const uint32_t rank = running + before + __popc(ball & ((1u << lane) - 1u));
             a.rank[i] = rank;
             if (rank < a.cap_spots) {
                 const SpotAcc r = a.acc[i];
@@ -98,6 +110,7 @@ __global__ void __launch_bounds__(256) cc3_finalize_kernel(const CC3Args a) {
                 a.sums[4ull * rank + 3] = r.sum_zi;
             }
         }
+        running += all;
     }
     if (threadIdx.x == 0) *a.n_components = running;
 }
