@@ -136,16 +136,19 @@ def merge_slabs(slabs: list[SlabResult], width: int, height: int, with_sums: boo
             absm[r] += absm[i]
     # Reflection3D::center_of_mass / peak_centroid_distance, recomputed from the exact sums for
     # every surviving spot: merged ones changed, and slab-local z became sweep z for the rest
-    for r in np.flatnonzero(roots == np.arange(n)):
-        wt = float(sums[r, 0])
-        s = spots[r]
-        if wt == 0:
-            s["com_x"] = s["com_y"] = s["com_z"] = s["peak_centroid_distance"] = np.nan
-            continue
-        com = [np.float32((float(sums[r, k]) * 0.5) / wt) for k in (1, 2, 3)]
-        s["com_x"], s["com_y"], s["com_z"] = com
-        d = [np.float32(np.float32(s[f]) + np.float32(0.5)) - c for f, c in zip(("peak_x", "peak_y", "peak_z"), com)]
-        s["peak_centroid_distance"] = np.sqrt(np.float32(np.float32(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]))
+    # (vectorised; int -> float64 rounds to nearest exactly as the C++ static_cast<double> does)
+    alive = np.flatnonzero(roots == np.arange(n))
+    f64 = np.array([[float(v) for v in sums[r]] for r in alive], dtype=np.float64).reshape(-1, 4)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        com = [((f64[:, k] * 0.5) / f64[:, 0]).astype(np.float32) for k in (1, 2, 3)]
+        d = [(spots[f][alive].astype(np.float32) + np.float32(0.5)) - c
+             for f, c in zip(("peak_x", "peak_y", "peak_z"), com)]
+        dist = np.sqrt((d[0] * d[0] + d[1] * d[1]).astype(np.float32) + d[2] * d[2]).astype(np.float32)
+    zero = f64[:, 0] == 0
+    for arr in (*com, dist):
+        arr[zero] = np.nan
+    spots["com_x"][alive], spots["com_y"][alive], spots["com_z"][alive] = com
+    spots["peak_centroid_distance"][alive] = dist
     keep = roots == np.arange(n)
     out = spots[keep]
     order = np.argsort(out["label"], kind="stable")
