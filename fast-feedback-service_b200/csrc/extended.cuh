@@ -40,43 +40,60 @@ __global__ void __launch_bounds__(256) erode_kernel(const ErodeArgs a) {
     const int n_words = wpr * a.height;
     const int last_word = (a.width - 1) >> 5;
     const uint32_t last_valid = (a.width & 31) ? ((1u << (a.width & 31)) - 1u) : 0xffffffffu;
-    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_words; t += gridDim.x * blockDim.x) {
+    const int lane = threadIdx.x & 31;
+    // warp-uniform trip count: the candidate push below is a warp-aggregated append (one
+    // atomic per warp and word row instead of one per core pixel on a single address)
+    for (int t0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); t0 < n_words; t0 += gridDim.x * blockDim.x) {
+        const int t = t0 + lane;
         const int row = t / wpr, wi = t - row * wpr;
-        uint32_t core = 0xffffffffu;
-        if (wi > last_word) {
+        const bool in_plane = t < n_words;
+        uint32_t core = 0;
+        if (in_plane && wi > last_word) {
             B[t] = 0;
-            continue;
-        }
-        // out-of-image pixels are ignored by the distance transform: they read as "true"
-        auto word = [&](int r, int w) -> uint32_t {
-            if (r < 0 || r >= a.height || w < 0 || w > last_word) return 0xffffffffu;
-            uint32_t v = D[(size_t)r * wpr + w];
-            if (w == last_word) v |= ~last_valid;
-            return v;
-        };
+        } else if (in_plane) {
+            core = 0xffffffffu;
+            // out-of-image pixels are ignored by the distance transform: they read as "true"
+            auto word = [&](int r, int w) -> uint32_t {
+                if (r < 0 || r >= a.height || w < 0 || w > last_word) return 0xffffffffu;
+                uint32_t v = D[(size_t)r * wpr + w];
+                if (w == last_word) v |= ~last_valid;
+                return v;
+            };
 #pragma unroll
-        for (int dr = -2; dr <= 2; ++dr) {
-            const int r = row + dr;
-            const uint32_t c = word(r, wi), l = word(r, wi - 1), rt = word(r, wi + 1);
-            // bit i of the result = AND of bits i-2 .. i+2 of the row
-            uint32_t h = c;
-            h &= (c << 1) | (l >> 31);
-            h &= (c << 2) | (l >> 30);
-            h &= (c >> 1) | (rt << 31);
-            h &= (c >> 2) | (rt << 30);
-            core &= h;
+            for (int dr = -2; dr <= 2; ++dr) {
+                const int r = row + dr;
+                const uint32_t c = word(r, wi), l = word(r, wi - 1), rt = word(r, wi + 1);
+                // bit i of the result = AND of bits i-2 .. i+2 of the row
+                uint32_t h = c;
+                h &= (c << 1) | (l >> 31);
+                h &= (c << 2) | (l >> 30);
+                h &= (c >> 1) | (rt << 31);
+                h &= (c >> 2) | (rt << 30);
+                core &= h;
+            }
+            const uint32_t m = a.mask_bits[t];
+            const uint32_t valid_cols = wi == last_word ? last_valid : 0xffffffffu;
+            core &= m & valid_cols;  // the centre itself is in D (dr = 0), D implies mask
+            B[t] = m & ~core & valid_cols;
         }
-        const uint32_t m = a.mask_bits[t];
-        const uint32_t valid_cols = wi == last_word ? last_valid : 0xffffffffu;
-        core &= m & valid_cols;  // the centre itself is in D (dr = 0), D implies mask
-        B[t] = m & ~core & valid_cols;
         // core pixels are the only possible strong pixels of the final pass
-        uint32_t bits = core;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const unsigned slot = atomicAdd(a.cand_count + z, 1u);
-            if (slot < a.cand_cap) a.cand[(size_t)z * a.cand_cap + slot] = (uint32_t)(wi * 32 + b) | ((uint32_t)row << 13);
+        if (__any_sync(0xffffffffu, core != 0)) {
+            const uint32_t cnt = __popc(core);
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, off);
+                if (lane >= off) incl += v;
+            }
+            uint32_t base = 0;
+            if (lane == 31) base = atomicAdd(a.cand_count + z, incl);
+            base = __shfl_sync(0xffffffffu, base, 31);
+            uint32_t slot = base + incl - cnt;
+            for (uint32_t bits = core; bits; bits &= bits - 1, ++slot) {
+                const int b = __ffs(bits) - 1;
+                if (slot < a.cand_cap)
+                    a.cand[(size_t)z * a.cand_cap + slot] = (uint32_t)(wi * 32 + b) | ((uint32_t)row << 13);
+            }
         }
     }
 }
