@@ -426,7 +426,7 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
 
 template <typename PixelT>
 static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
-    static const int w = env_int("FFS_FUSED_WARPS", 3);  // warps (independent tasks) per CTA
+    static const int w = env_int("FFS_FUSED_WARPS", sizeof(PixelT) == 2 ? 4 : 3);  // warps (independent tasks) per CTA
     static const int stg = env_int("FFS_FUSED_STAGES", 2);
     if (stg == 2) {
         switch (w) {
@@ -434,14 +434,16 @@ static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
             case 2: return launch_fused_w<PixelT, 2, 2>(c, first_slot, n, st);
             case 4: return launch_fused_w<PixelT, 4, 2>(c, first_slot, n, st);
             case 5: return launch_fused_w<PixelT, 5, 2>(c, first_slot, n, st);
-            default: return launch_fused_w<PixelT, 3, 2>(c, first_slot, n, st);
+            case 3: return launch_fused_w<PixelT, 3, 2>(c, first_slot, n, st);
+            default: return launch_fused_w<PixelT, 2, 2>(c, first_slot, n, st);
         }
     }
     switch (w) {
         case 1: return launch_fused_w<PixelT, 1, 3>(c, first_slot, n, st);
         case 2: return launch_fused_w<PixelT, 2, 3>(c, first_slot, n, st);
         case 4: return launch_fused_w<PixelT, 4, 3>(c, first_slot, n, st);
-        default: return launch_fused_w<PixelT, 3, 3>(c, first_slot, n, st);
+        case 3: return launch_fused_w<PixelT, 3, 3>(c, first_slot, n, st);
+        default: return launch_fused_w<PixelT, 2, 3>(c, first_slot, n, st);
     }
 }
 

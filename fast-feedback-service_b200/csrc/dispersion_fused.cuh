@@ -37,11 +37,11 @@ namespace ffsb {
 #ifndef FUSED_DEBUG_MODES
 #define FUSED_DEBUG_MODES 0  // 1: FFS_FUSED_DEBUG=5 (TMA only) is honoured by the streaming loop
 #endif
+#ifndef FUSED_ROWS_PER_BATCH
+#define FUSED_ROWS_PER_BATCH 2  // measured: 4 is no faster at equal occupancy and costs 18 registers
+#endif
 #ifndef FUSED_DP2A
 #define FUSED_DP2A 1
-#endif
-#ifndef FUSED_MIN_WARPS_PER_SM
-#define FUSED_MIN_WARPS_PER_SM 12  // register cap = 65536 / (32 * this)
 #endif
 
 template <typename PixelT>
@@ -62,12 +62,17 @@ struct FusedGeo {
     static constexpr int RING_ROWS = 2 * SR;
     static constexpr int RING_ROW_BYTES = 32 * 16;
     static constexpr int RING_BYTES = RING_ROWS * RING_ROW_BYTES;
+    // resident warps per SM the kernel is compiled for (register cap = 65536 / (32 * this)):
+    // 16-bit: 4 CTAs of 4 warps at 128 registers and 13.8 KB of shared memory per warp; the
+    // 32-bit front end needs more registers
+    static constexpr int MIN_WARPS_PER_SM = sizeof(PixelT) == 2 ? 16 : 12;
     static constexpr int GQ_CAP = 96;        // pending candidate groups (< 32 + 2 rows * 30)
     static constexpr int PQ_CAP = 320;       // pending candidate pixels, both kinds (< 32 + 32 + 32 * 8)
-    // per queued group: 4 B meta + 32 B window sums + 16 B clamped centre-row words
+    // per queued group: 4 B meta + 32 B window sums (the centre-row pixels are re-read from the
+    // frame in stage 2: carrying them cost 1.5 KB of shared memory per warp, i.e. occupancy)
     // plus one double-ended pixel queue: pixels whose window is fully valid (fast exact test)
     // grow from the bottom, all others from the top
-    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32 + 16) + PQ_CAP * 4;
+    static constexpr int QUEUE_BYTES = GQ_CAP * (4 + 32) + PQ_CAP * 4;
     static_assert(RING_ROWS > 2 * KH, "ring must hold the 7-row window");
     static_assert(IMG_STAGE_BYTES % 128 == 0 && QUEUE_BYTES % 128 == 0, "TMA destination alignment");
     __host__ __device__ static constexpr int smem_per_warp(int stages) {
@@ -178,8 +183,7 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
     const int lane = threadIdx.x & 31;
     uint32_t* gq = reinterpret_cast<uint32_t*>(qbase);
     uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);
-    uint4* cq = hq + 2 * G::GQ_CAP;
-    uint32_t* pq = reinterpret_cast<uint32_t*>(cq + G::GQ_CAP);  // [0, pqn): pixels with a full 7x7 window
+    uint32_t* pq = reinterpret_cast<uint32_t*>(hq + 2 * G::GQ_CAP);  // [0, pqn): pixels with a full 7x7 window
     uint32_t* pg = pq + G::PQ_CAP - 1;                           // pg[-k], k < pgn: pixels near the mask / the edge
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
     const uint8_t* valid = a.valid_bits;
@@ -216,19 +220,19 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
             col0 = x0 + (int)(e & 31u) * PPL;
             row = r0 + (int)((e >> 5) & 0x1ffu);
             uint32_t v[8], vb = 0xffu;
-            if constexpr (sizeof(PixelT) == 2) {
-                // masked + clamped centre-row values queued by the streaming loop: a masked pixel
-                // reads 0 and never passes; a clamped one (== CLAMP) always passes (see below)
-                const uint4 cw = cq[qi];
-                v[0] = cw.x & 0xffffu; v[1] = cw.x >> 16; v[2] = cw.y & 0xffffu; v[3] = cw.y >> 16;
-                v[4] = cw.z & 0xffffu; v[5] = cw.z >> 16; v[6] = cw.w & 0xffffu; v[7] = cw.w >> 16;
-            } else {
-                // 32-bit pixels >= 2^24 are not in the clamped words (they count 0): read the frame
+            {
+                // the centre row's raw pixels and validity bits, from the frame (L2 hits)
                 vb = valid[(size_t)row * a.valid_pitch + (col0 >> 3)];
                 const PixelT* p = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch) + col0;
-                const uint4 ra = reinterpret_cast<const uint4*>(p)[0], rb = reinterpret_cast<const uint4*>(p)[1];
-                v[0] = ra.x; v[1] = ra.y; v[2] = ra.z; v[3] = ra.w;
-                v[4] = rb.x; v[5] = rb.y; v[6] = rb.z; v[7] = rb.w;
+                if constexpr (sizeof(PixelT) == 2) {
+                    const uint4 cw = reinterpret_cast<const uint4*>(p)[0];
+                    v[0] = cw.x & 0xffffu; v[1] = cw.x >> 16; v[2] = cw.y & 0xffffu; v[3] = cw.y >> 16;
+                    v[4] = cw.z & 0xffffu; v[5] = cw.z >> 16; v[6] = cw.w & 0xffffu; v[7] = cw.w >> 16;
+                } else {
+                    const uint4 ra = reinterpret_cast<const uint4*>(p)[0], rb = reinterpret_cast<const uint4*>(p)[1];
+                    v[0] = ra.x; v[1] = ra.y; v[2] = ra.z; v[3] = ra.w;
+                    v[4] = rb.x; v[5] = rb.y; v[6] = rb.z; v[7] = rb.w;
+                }
             }
             // per-pixel bound: the pixel's own window sum (still a lower bound of x) over m_ub
 #pragma unroll
@@ -237,7 +241,6 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
                 float sq;
                 asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
                 uint32_t T = (uint32_t)max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
-                if constexpr (sizeof(PixelT) == 2) T = min(T, G::CLAMP - 1u);
                 bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
             }
         }
@@ -289,12 +292,13 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
 }
 
 template <typename PixelT, int STAGES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
+__global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM / WARPS)
   fused_dispersion_kernel(const __grid_constant__ CUtensorMap tm_img,
                           const __grid_constant__ CUtensorMap tm_info,
                           const __grid_constant__ ThreshArgs a) {
     using G = FusedGeo<PixelT>;
-    constexpr int SR = G::SR, KH = G::KH, PPL = G::PPL;
+    constexpr int SR = G::SR, KH = G::KH, PPL = G::PPL, RB = FUSED_ROWS_PER_BATCH;
+    static_assert(SR % RB == 0 && RB % 2 == 0, "the queue is checked every two rows");
     static_assert(SR == 4, "row loop is written for 4-row stages and an 8-row ring");
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -323,8 +327,8 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
     uint8_t* ring = wsm + STAGES * G::STAGE_BYTES;
     uint32_t* gq = reinterpret_cast<uint32_t*>(ring + G::RING_BYTES);
     uint4* hq = reinterpret_cast<uint4*>(gq + G::GQ_CAP);   // 2 x uint4 per queued group: its 8 window sums
-    uint4* cq = hq + 2 * G::GQ_CAP;                         // its clamped centre-row words
     uint64_t* bars = reinterpret_cast<uint64_t*>(ring + G::RING_BYTES + G::QUEUE_BYTES);
+    static_assert(G::QUEUE_BYTES % 128 == 0, "mbarrier alignment");
 
     const int r0 = rt * a.tile_rows;
     const int row_end = min(r0 + a.tile_rows, a.height);
@@ -384,10 +388,14 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
         {
         // The stage body is written in three straight-line phases so that the four rows'
         // dependent chains (LDS -> sums -> SHFL -> sums -> MUFU -> VOTE) interleave.
-        // ---- phase A: load, mask, clamp, vertical running sums, ring update ------------------
-        uint32_t Vs[SR][4], vmc[SR], mub[SR];
+        // FUSED_ROWS_PER_BATCH rows at a time (4: one batch per stage; 2: two, fewer live registers)
 #pragma unroll
-        for (int u = 0; u < SR; ++u) {
+        for (int hb = 0; hb < SR / RB; ++hb) {
+        // ---- phase A: load, mask, clamp, vertical running sums, ring update ------------------
+        uint32_t Vs[RB][4], vmc[RB], mub[RB];
+#pragma unroll
+        for (int uu = 0; uu < RB; ++uu) {
+            const int u = hb * RB + uu;  // row of the stage
             uint32_t c[4], vm, info;
             fused_load_row<PixelT>(st + u * G::IMG_ROW_BYTES + pimg_off, st + pinfo_off + u * G::INFO_ROW_BYTES,
                                    c, vm, info);
@@ -400,23 +408,24 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             V[3] = V[3] + c[3] - old.w;
             *reinterpret_cast<uint4*>(rcur + u * G::RING_ROW_BYTES) = make_uint4(c[0], c[1], c[2], c[3]);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) Vs[u][k] = V[k];
-            vmc[u] = hv3;          // centre row (i - 3): max masked value and m_ub
-            mub[u] = hi3 >> 8;
+            for (int k = 0; k < 4; ++k) Vs[uu][k] = V[k];
+            vmc[uu] = hv3;          // centre row (i - 3): max masked value and m_ub
+            mub[uu] = hi3 >> 8;
             hv3 = hv2; hv2 = hv1; hv1 = vm;
             hi3 = hi2; hi2 = hi1; hi1 = info;
         }
         // ---- phase B: horizontal sums, group threshold, pass flag (no branches) --------------
-        uint32_t Hx[SR][8];
-        unsigned ball[SR];
+        uint32_t Hx[RB][8];
+        unsigned ball[RB];
 #pragma unroll
-        for (int u = 0; u < SR; ++u) {
+        for (int uu = 0; uu < RB; ++uu) {
+            const int u = hb * RB + uu;  // row of the stage
             const int i = g * SR + u;  // load-row index within the task
             const int out_row = r0 + i - 2 * KH;
-            const uint32_t l2 = __shfl_up_sync(0xffffffffu, Vs[u][2], 1);
-            const uint32_t l3 = __shfl_up_sync(0xffffffffu, Vs[u][3], 1);
-            const uint32_t rr0 = __shfl_down_sync(0xffffffffu, Vs[u][0], 1);
-            const uint32_t rr1 = __shfl_down_sync(0xffffffffu, Vs[u][1], 1);
+            const uint32_t l2 = __shfl_up_sync(0xffffffffu, Vs[uu][2], 1);
+            const uint32_t l3 = __shfl_up_sync(0xffffffffu, Vs[uu][3], 1);
+            const uint32_t rr0 = __shfl_down_sync(0xffffffffu, Vs[uu][0], 1);
+            const uint32_t rr1 = __shfl_down_sync(0xffffffffu, Vs[uu][1], 1);
 #if FUSED_DP2A
             // 7-tap sums of 16-bit halves with IDP.2A (d = c + a.lo * b0 + a.hi * b1): the
             // integer dot product issues on the FMA pipe, which this loop otherwise leaves idle,
@@ -424,23 +433,23 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             // Words: W0 = l2, W1 = l3, W2..W5 = own V[0..3], W6 = rr0, W7 = rr1; window j = halves j .. j+6
             // of the 16-half sequence, starting at W0.hi.
             constexpr uint32_t LO = 0x0001u, HI = 0x0100u, BOTH = 0x0101u;
-            const uint32_t* Wv = Vs[u];
+            const uint32_t* Wv = Vs[uu];
             const uint32_t a23 = __dp2a_lo(Wv[0], BOTH, __dp2a_lo(Wv[1], BOTH, 0u));
             const uint32_t a45 = __dp2a_lo(Wv[2], BOTH, __dp2a_lo(Wv[3], BOTH, 0u));
             const uint32_t t1 = __dp2a_lo(l3, BOTH, a23);      // W1 + W2 + W3
             const uint32_t t2 = __dp2a_lo(Wv[2], BOTH, a23);   // W2 + W3 + W4
             const uint32_t t3 = __dp2a_lo(Wv[1], BOTH, a45);   // W3 + W4 + W5
             const uint32_t t4 = __dp2a_lo(rr0, BOTH, a45);     // W4 + W5 + W6
-            Hx[u][0] = __dp2a_lo(l2, HI, t1);
-            Hx[u][1] = __dp2a_lo(Wv[2], LO, t1);
-            Hx[u][2] = __dp2a_lo(l3, HI, t2);
-            Hx[u][3] = __dp2a_lo(Wv[3], LO, t2);
-            Hx[u][4] = __dp2a_lo(Wv[0], HI, t3);
-            Hx[u][5] = __dp2a_lo(rr0, LO, t3);
-            Hx[u][6] = __dp2a_lo(Wv[1], HI, t4);
-            Hx[u][7] = __dp2a_lo(rr1, LO, t4);
-            const uint32_t xmin = min(min(min(Hx[u][0], Hx[u][1]), min(Hx[u][2], Hx[u][3])),
-                                      min(min(Hx[u][4], Hx[u][5]), min(Hx[u][6], Hx[u][7])));
+            Hx[uu][0] = __dp2a_lo(l2, HI, t1);
+            Hx[uu][1] = __dp2a_lo(Wv[2], LO, t1);
+            Hx[uu][2] = __dp2a_lo(l3, HI, t2);
+            Hx[uu][3] = __dp2a_lo(Wv[3], LO, t2);
+            Hx[uu][4] = __dp2a_lo(Wv[0], HI, t3);
+            Hx[uu][5] = __dp2a_lo(rr0, LO, t3);
+            Hx[uu][6] = __dp2a_lo(Wv[1], HI, t4);
+            Hx[uu][7] = __dp2a_lo(rr1, LO, t4);
+            const uint32_t xmin = min(min(min(Hx[uu][0], Hx[uu][1]), min(Hx[uu][2], Hx[uu][3])),
+                                      min(min(Hx[uu][4], Hx[uu][5]), min(Hx[uu][6], Hx[uu][7])));
 #else
             uint32_t E[14];
             E[0] = l2 >> 16;
@@ -448,47 +457,45 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
             E[2] = l3 >> 16;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                E[3 + 2 * k] = Vs[u][k] & 0xffffu;
-                E[4 + 2 * k] = Vs[u][k] >> 16;
+                E[3 + 2 * k] = Vs[uu][k] & 0xffffu;
+                E[4 + 2 * k] = Vs[uu][k] >> 16;
             }
             E[11] = rr0 & 0xffffu;
             E[12] = rr0 >> 16;
             E[13] = rr1 & 0xffffu;
-            Hx[u][0] = E[0] + E[1] + E[2] + E[3] + E[4] + E[5] + E[6];
-            uint32_t xmin = Hx[u][0];
+            Hx[uu][0] = E[0] + E[1] + E[2] + E[3] + E[4] + E[5] + E[6];
+            uint32_t xmin = Hx[uu][0];
 #pragma unroll
             for (int j = 1; j < 8; ++j) {
-                Hx[u][j] = Hx[u][j - 1] + E[j + 6] - E[j - 1];
-                xmin = min(xmin, Hx[u][j]);
+                Hx[uu][j] = Hx[uu][j - 1] + E[j + 6] - E[j - 1];
+                xmin = min(xmin, Hx[uu][j]);
             }
 #endif
             // group threshold on the raw value: T = floor(mu + nsig_s' sqrt(mu)), mu = x_lb / m_ub
-            const float mu = (float)xmin * rcp_tab[mub[u]];
+            const float mu = (float)xmin * rcp_tab[mub[uu]];
             float sq;
             asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
             const int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
-            ball[u] = __ballot_sync(0xffffffffu,
-                                    out_lane && vmc[u] > (uint32_t)T && i >= 2 * KH && out_row < row_end);
+            ball[uu] = __ballot_sync(0xffffffffu,
+                                    out_lane && vmc[uu] > (uint32_t)T && i >= 2 * KH && out_row < row_end);
         }
         // poll the next stage's barrier now; the answer arrives while phase C runs
-        {
+        if (hb == SR / RB - 1) {
             const int sn = (s + 1 == STAGES) ? 0 : s + 1;
             ready = g + 1 < n_groups && ptx::mbar_try_wait(bars + sn, (s + 1 == STAGES) ? phase ^ 1u : phase);
         }
         // ---- phase C: queue the passing groups (predicated stores, no divergence); resolve
         // when 32 are pending -- checked every two rows, which GQ_CAP allows for ----------------
-        const uint32_t gq_s = ptx::smem_u32(gq), hq_s = ptx::smem_u32(hq), cq_s = ptx::smem_u32(cq);
+        const uint32_t gq_s = ptx::smem_u32(gq), hq_s = ptx::smem_u32(hq);
 #pragma unroll
-        for (int u = 0; u < SR; ++u) {
-            const bool p = (ball[u] >> lane) & 1u;
-            const int qi = qn + __popc(ball[u] & lt_mask);
-            // ring slot of the centre row i-3 is (i + 5) & 7
-            const uint4 cw = ptx::lds128((u < SR - 1) ? roth + (u + 1) * G::RING_ROW_BYTES : rcur);
-            ptx::sts32_if(p, gq_s + 4 * qi, (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[u] << 14));
-            ptx::sts128_if(p, hq_s + 32 * qi, Hx[u][0], Hx[u][1], Hx[u][2], Hx[u][3]);
-            ptx::sts128_if(p, hq_s + 32 * qi + 16, Hx[u][4], Hx[u][5], Hx[u][6], Hx[u][7]);
-            ptx::sts128_if(p, cq_s + 16 * qi, cw.x, cw.y, cw.z, cw.w);
-            qn += __popc(ball[u]);
+        for (int uu = 0; uu < RB; ++uu) {
+            const int u = hb * RB + uu;  // row of the stage
+            const bool p = (ball[uu] >> lane) & 1u;
+            const int qi = qn + __popc(ball[uu] & lt_mask);
+            ptx::sts32_if(p, gq_s + 4 * qi, (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[uu] << 14));
+            ptx::sts128_if(p, hq_s + 32 * qi, Hx[uu][0], Hx[uu][1], Hx[uu][2], Hx[uu][3]);
+            ptx::sts128_if(p, hq_s + 32 * qi + 16, Hx[uu][4], Hx[uu][5], Hx[uu][6], Hx[uu][7]);
+            qn += __popc(ball[uu]);
             if ((u & 1) && qn >= 32) {
                 __syncwarp();
                 do {
@@ -499,6 +506,7 @@ __global__ void __launch_bounds__(WARPS * 32, FUSED_MIN_WARPS_PER_SM / WARPS)
                 } while (qn >= 32);
             }
         }
+                }
         }
         // refill the stage we just consumed
         // Every lane's reads of this stage have completed (their values were consumed above) and
