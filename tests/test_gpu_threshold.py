@@ -67,6 +67,20 @@ def test_dispersion_background_at_and_above_the_clamp(lam, mask_kind, dtype):
     assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
 
 
+@pytest.mark.parametrize("lam", [0.02, 0.1, 0.5, 1.0])
+@pytest.mark.parametrize("nsig_b", [6.0, 1.0, 0.0])
+def test_dispersion_sparse_background(lam, nsig_b):
+    """Background far below one count per pixel: nearly every non-zero pixel passes the signal
+    bound and reaches the exact test; parity must hold for any nsig_b."""
+    img, mask = random_frame(200, 520, np.uint16, seed=int(lam * 100) + 3, lam=lam, n_spots=25, mask_kind="modules")
+    img[50:53, 100:140] = np.where(mask[50:53, 100:140] != 0, 1, img[50:53, 100:140])  # runs of single counts
+    img[120, 200:230:2] = np.where(mask[120, 200:230:2] != 0, 3, img[120, 200:230:2])
+    want = oracle.dispersion(img, mask, oracle.default_params(nsig_b=nsig_b))
+    got = run_gpu(img, mask, nsig_b=nsig_b)
+    assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
+    assert want.sum() > 0
+
+
 def test_dispersion_all_zero_all_masked_no_mask():
     h, w = 60, 300
     z = np.zeros((h, w), np.uint16)

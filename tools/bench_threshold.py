@@ -10,7 +10,8 @@ dtype = np.uint32 if os.environ.get("BPP", "2") == "4" else np.uint16
 nslots = int(os.environ.get("SLOTS", "8"))
 algo = os.environ.get("ALGO", "dispersion")
 mask = synth.make_mask(geom)
-frames = np.stack([synth.make_frame(geom, mask, dtype, 2, i) for i in range(min(nslots, 4))])
+bg = float(os.environ.get("BG", "2.0"))  # Poisson background level
+frames = np.stack([synth.make_frame(geom, mask, dtype, 2, i, background=bg) for i in range(min(nslots, 4))])
 frames = np.concatenate([frames] * ((nslots + len(frames) - 1) // len(frames)))[:nslots]
 sf = Spotfinder(geom.width, geom.height, dtype, mask, n_slots=nslots, algorithm=algo)
 sf.upload(frames)
