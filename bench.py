@@ -129,7 +129,7 @@ def run_reference_arm(args):
     sample = (f"{per_step} frames/step x {args.steps} steps, frame-parallel over {T} threads; threshold = "
               f"{'reference standalone.cc compiled in place' if cpu.kind == 'reference' else 'oracle port'}, "
               "CC + filters = oracle port")
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -137,7 +137,7 @@ def run_reference_arm(args):
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": T, "kind": cpu.kind, "sample": sample},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }), flush=True)
+    }))
 
 
 def workload_config(batch):
@@ -394,13 +394,36 @@ def run_gpu_arm(args):
                                    "sample": f"{n} frames frame-parallel over {T} host threads; threshold = "
                                              f"{'reference standalone.cc (oracle/_ref)' if cpu.kind == 'reference' else 'oracle port'}"
                                              ", CC + filters = oracle port"}
-        print(json.dumps(out), flush=True)
+        emit(out)
     sf.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its
+    version banner on first use), so keep the real stdout for the result and point fd 1 at
+    stderr for everything else."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, line)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
