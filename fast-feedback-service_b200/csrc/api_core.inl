@@ -194,6 +194,7 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_valid_bits);
     cudaFree(c->d_info);
     cudaFree(c->d_mcount);
+    cudaFree(c->d_gain);
     cudaFree(c->d_frames);
     cudaFree(c->d_strong);
     cudaFree(c->d_ext1);
@@ -237,6 +238,47 @@ extern "C" size_t ffs_frame_pitch(const ffs_ctx* c) { return c ? c->pitch : 0; }
 extern "C" size_t ffs_frame_bytes_device(const ffs_ctx* c) { return c ? c->frame_stride : 0; }
 extern "C" uint64_t ffs_mask_valid_count(ffs_ctx* c) { return c ? c->valid_count : 0; }
 extern "C" void ffs_free(void* p) { free(p); }
+
+// threshold_w_gain (baseline.cpp:289-310): a per-pixel gain map for the standard dispersion test.
+extern "C" int ffs_set_gain(ffs_ctx* c, const double* gain) {
+    if (!c) return FFS_ERR_ARG;
+    if (c->p.algorithm != FFS_ALGO_DISPERSION) {
+        c->err = "ffs_set_gain: only the standard dispersion algorithm takes a gain map";
+        return FFS_ERR_ARG;
+    }
+    FFS_CK(c, cudaSetDevice(c->p.device));
+    FFS_CK(c, cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lk(c->mu);
+    for (auto& s : c->slots)  // the slot graphs captured the old launch parameters
+        for (auto& g : s.graph)
+            if (g) {
+                cudaGraphExecDestroy(g);
+                g = nullptr;
+            }
+    if (!gain) {
+        cudaFree(c->d_gain);
+        c->d_gain = nullptr;
+        c->gain_min = 1.0;
+        c->gain_brute = false;
+        return FFS_OK;
+    }
+    const size_t n = (size_t)c->p.width * c->p.height;
+    std::vector<uint8_t> mask(n);
+    FFS_CK(c, cudaMemcpy(mask.data(), c->d_mask, n, cudaMemcpyDeviceToHost));
+    double gmin = INFINITY;
+    bool bad = false;
+    for (size_t k = 0; k < n; ++k) {
+        if (!mask[k]) continue;
+        const double g = gain[k];
+        if (!(g > 0.0) || !std::isfinite(g)) bad = true;
+        else gmin = std::min(gmin, g);
+    }
+    if (!c->d_gain) FFS_CK(c, cudaMalloc(&c->d_gain, n * sizeof(double)));
+    FFS_CK(c, cudaMemcpy(c->d_gain, gain, n * sizeof(double), cudaMemcpyHostToDevice));
+    c->gain_min = std::isfinite(gmin) ? gmin : 1.0;
+    c->gain_brute = bad;  // sqrt of a non-positive gain: the reference yields NaN there; decide every pixel exactly
+    return FFS_OK;
+}
 
 extern "C" int ffs_apply_resolution_mask(ffs_ctx* c, float wavelength, float distance_m, float bcx,
                                          float bcy, float psx, float psy, float dmin, float dmax) {
@@ -310,13 +352,16 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.cand = c->d_cand;
     a.cand_count = c->d_cand_count;
     a.cand_cap = c->cand_cap;
-    a.force_brute = env_int("FFS_FORCE_BRUTE", 0);
+    a.force_brute = env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute;
     a.nsig_b = c->p.nsig_b;
     a.nsig_s = c->p.nsig_s;
     a.threshold = c->p.threshold;
     a.min_count = c->eff_min_count;
     a.prefilter_k = (float)(c->p.nsig_s * c->p.nsig_s * (1.0 - 1e-4));
-    a.sig_k = (float)(c->p.nsig_s * (1.0 - 1e-4));
+    // with a gain map b > d reads v > mu + nsig_s sqrt(g) sqrt(mu): the smallest gain keeps the
+    // pruning bound a lower bound
+    a.sig_k = (float)(c->p.nsig_s * std::sqrt(c->d_gain ? c->gain_min : 1.0) * (1.0 - 1e-4));
+    a.gain = c->d_gain;
     a.thr_floor = (int)std::min(std::floor(c->p.threshold), 1073741824.0);
     a.mcount = c->d_mcount;
     a.m_pitch = c->m_pitch;
@@ -456,7 +501,7 @@ static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
                               sizeof(uint32_t) * c->n_chunks * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
     static const int two_kernel = env_int("FFS_TWO_KERNEL", 0);  // A/B: the round-1 prefilter + resolve pair
-    if (two_kernel || env_int("FFS_FORCE_BRUTE", 0)) {
+    if (two_kernel || env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute) {
         if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
         return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);
     }

@@ -57,6 +57,9 @@ struct ffs_ctx {
     uint8_t* d_valid_bits = nullptr;  // 1-bit validity plane
     uint8_t* d_info = nullptr;        // per group of 8 pixels: {validity byte, m_ub} (dispersion_fused.cuh)
     size_t info_pitch = 0;            // bytes per row of d_info (multiple of 16)
+    double* d_gain = nullptr;         // optional gain map (ffs_set_gain), width*height
+    double gain_min = 1.0;            // over the mask-valid pixels: scales the pruning bound
+    bool gain_brute = false;          // gain map with non-positive / non-finite entries: no pruning
     uint8_t* d_mcount = nullptr;      // per pixel: valid pixels in its clipped 7x7 window (extended_stream.cuh)
     size_t m_pitch = 0;
     uint8_t* d_frames = nullptr;      // n_slots pitched frames

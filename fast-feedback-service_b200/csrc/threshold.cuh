@@ -60,6 +60,8 @@ struct ThreshArgs {
     int thr_floor;      // floor(threshold): v > threshold <=> v > thr_floor for integer v
     uint32_t* chunk_count;  // per slot: strong pixels per 1024-word chunk of the strong plane (the
     int n_chunks;           // connected-components compaction's first pass); NULL = do not count
+    const double* gain;     // optional per-pixel gain map, width*height row-major (threshold_w_gain,
+                            // baseline.cpp:187-250); NULL = the plain test
     const uint8_t* mcount;  // per pixel: mask-valid pixels in its image-clipped 7x7 window
     size_t m_pitch;         // (group_info_kernel); 49 <=> window inside the image and fully valid
 };
@@ -100,6 +102,36 @@ struct ThreshGeo {
 // Exact evaluation of one pixel: integer window gather + fp64 test in the reference's
 // operation order.  extended_pass1 = true gives DispersionExtendedThreshold's first pass
 // (baseline.cpp:465-469: "a > c" only, no global threshold, no signal test).
+// The fp64 decision from exact integer window sums, in the reference's operation order
+// (standalone.cc:164-170; with a gain map baseline.cpp:240-246).  min_count is checked by the
+// caller's common prologue here as well so that every resolve routine shares one copy.
+__device__ __forceinline__ bool dispersion_decide(const ThreshArgs& a, uint32_t m, uint32_t x,
+                                                  unsigned long long y, uint32_t v, int col, int row) {
+    const double vd = (double)v, md = (double)m, xd = (double)x, yd = (double)y;
+    if (!((int)m >= a.min_count)) return false;
+    if (!(vd > a.threshold)) return false;
+    const double b = __dsub_rn(__dmul_rn(md, vd), xd);
+    if (a.gain) {
+        // double a = m * y - x * x;  double c = gain[k] * x * (m - 1 + nsig_b_ * std::sqrt(2 * (m - 1)));
+        // double d = nsig_s_ * std::sqrt(gain[k] * x * m);
+        const double g = a.gain[(size_t)row * a.width + col];
+        const double gx = __dmul_rn(g, xd);
+        const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(gx, md)));
+        if (!(b > d)) return false;
+        const double aa = __dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd));
+        const double m1 = __dsub_rn(md, 1.0);
+        const double cc = __dmul_rn(gx, __dadd_rn(m1, __dmul_rn(a.nsig_b, __dsqrt_rn(__dmul_rn(2.0, m1)))));
+        return aa > cc;
+    }
+    const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
+    if (!(b > d)) return false;
+    const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
+                                __dmul_rn(xd, __dsub_rn(md, 1.0)));
+    const double cc =
+      __dmul_rn(__dmul_rn(xd, a.nsig_b), __dsqrt_rn(__dmul_rn(2.0, __dsub_rn(md, 1.0))));
+    return aa > cc;
+}
+
 template <typename PixelT, int KH, bool EXT_PASS1>
 __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t* frame,
                                               const uint8_t* valid, int col, int row) {
@@ -131,6 +163,9 @@ __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t
             }
         }
     }
+    if (!EXT_PASS1)
+        return dispersion_decide(a, m, x, y, (uint32_t) reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col],
+                                 col, row);
     const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
     const double md = (double)m, xd = (double)x, yd = (double)y;
     // if (mask[k] && m >= min_count_ && x >= 0 && src[k] > threshold_)
@@ -210,18 +245,8 @@ __device__ __forceinline__ bool resolve_pixel_wide(const ThreshArgs& a, const ui
         }
         if constexpr (sizeof(PixelT) == 2) m += __popc(sel);
     }
-    const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
-    const double md = (double)m, xd = (double)x, yd = (double)y;
-    if (!((int)m >= a.min_count)) return false;
-    if (!(vd > a.threshold)) return false;
-    const double b = __dsub_rn(__dmul_rn(md, vd), xd);
-    const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
-    if (!(b > d)) return false;
-    const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
-                                __dmul_rn(xd, __dsub_rn(md, 1.0)));
-    const double cc =
-      __dmul_rn(__dmul_rn(xd, a.nsig_b), __dsqrt_rn(__dmul_rn(2.0, __dsub_rn(md, 1.0))));
-    return aa > cc;
+    const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    return dispersion_decide(a, m, x, y, vc, col, row);
 }
 
 // Exact test for a pixel whose 7x7 window lies inside the image and is fully mask-valid
@@ -286,18 +311,7 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
             }
         }
     }
-    const double vd = (double)vc;
-    const double md = (double)m, xd = (double)x, yd = (double)y;
-    if (!((int)m >= a.min_count)) return false;
-    if (!(vd > a.threshold)) return false;
-    const double b = __dsub_rn(__dmul_rn(md, vd), xd);
-    const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
-    if (!(b > d)) return false;
-    const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
-                                __dmul_rn(xd, __dsub_rn(md, 1.0)));
-    const double cc =
-      __dmul_rn(__dmul_rn(xd, a.nsig_b), __dsqrt_rn(__dmul_rn(2.0, __dsub_rn(md, 1.0))));
-    return aa > cc;
+    return dispersion_decide(a, m, x, y, vc, col, row);
 }
 
 __device__ __forceinline__ void set_strong(const ThreshArgs& a, int z, int col, int row) {

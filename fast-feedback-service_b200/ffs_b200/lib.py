@@ -120,6 +120,7 @@ SYMBOLS = {
     "ffs_sweep_finish": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_plane": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_sums": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_set_gain": (_i, [_vp, _vp]),
     "ffs_keep_pixel_lists": (_i, [_vp, _i]),
     "ffs_last_pixel_list": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_last_frame": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),

@@ -237,6 +237,17 @@ class Spotfinder:
         self._ck(self._L.ffs_wait(self._ctx, C.byref(res), spots.ctypes.data, max_spots, C.byref(n)), "ffs_wait")
         return res, spots[:min(n.value, max_spots)]
 
+    def set_gain(self, gain):
+        """Per-pixel gain map (H, W) float64 for the standard dispersion test (threshold_w_gain,
+        baseline.cpp:289-310); None removes it."""
+        if gain is None:
+            self._ck(self._L.ffs_set_gain(self._ctx, None), "ffs_set_gain")
+            return
+        g = np.ascontiguousarray(gain, dtype=np.float64)
+        if g.shape != (self.height, self.width):
+            raise ValueError("gain must be (height, width)")
+        self._ck(self._L.ffs_set_gain(self._ctx, g.ctypes.data), "ffs_set_gain")
+
     # -- rotation sweeps: 3D connected components --------------------------------------------
     def sweep_begin(self, max_frames: int = 0):
         self._ck(self._L.ffs_sweep_begin(self._ctx, max_frames), "ffs_sweep_begin")

@@ -187,6 +187,50 @@ int64_t ffs_oracle_dispersion(const void *image, int bpp, const uint8_t *mask, i
     return count;
 }
 
+/* DispersionThreshold::threshold_w_gain, baseline.cpp:289-310 with compute_threshold(table,
+ * src, mask, gain, dst) :187-250: same SAT, per-pixel gain map,
+ *     a = m*y - x*x;  b = m*src - x;
+ *     c = gain*x*(m - 1 + nsig_b*sqrt(2*(m - 1)));  d = nsig_s*sqrt(gain*x*m);
+ * PARITY UNPINNED (baseline.cpp needs DIALS/scitbx headers; no executable of the reference
+ * reaches this variant). */
+int64_t ffs_oracle_dispersion_gain(const void *image, int bpp, const uint8_t *mask, int width,
+                                   int height, const ffs_oracle_params *p, const double *gain,
+                                   uint8_t *dst) {
+    int rc = check_args(image, bpp, mask, width, height, p, dst);
+    if (rc) return rc;
+    if (!gain) return -1;
+    size_t n = (size_t)width * height;
+    double *src = frame_to_double(image, bpp, n);
+    sat_cell *table = (sat_cell *)malloc(n * sizeof(sat_cell));
+    if (!src || !table) {
+        free(src);
+        free(table);
+        return -10;
+    }
+    build_sat(table, src, mask, width, height);
+    int min_count = effective_min_count(p);
+    int64_t count = 0;
+    size_t k = 0;
+    for (int j = 0; j < height; ++j)
+        for (int i = 0; i < width; ++i, ++k) {
+            double m, x, y;
+            sat_window(table, width, height, i, j, p->kernel_half_x, p->kernel_half_y, &m, &x,
+                       &y);
+            dst[k] = 0;
+            if (mask[k] && m >= min_count && x >= 0 && src[k] > p->threshold) {
+                double a = m * y - x * x;
+                double b = m * src[k] - x;
+                double c = gain[k] * x * (m - 1 + p->nsig_b * sqrt(2 * (m - 1)));
+                double d = p->nsig_s * sqrt(gain[k] * x * m);
+                dst[k] = a > c && b > d;
+            }
+            count += dst[k];
+        }
+    free(table);
+    free(src);
+    return count;
+}
+
 /* chebyshev_distance(src, false, dst): DIALS 3.25 dials/algorithms/image/filter/
  * distance.h (un-vendored; call site baseline.cpp:558).  Published algorithm: a
  * two-pass 8-neighbour chamfer transform, out-of-image neighbours count as

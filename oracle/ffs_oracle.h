@@ -63,6 +63,10 @@ int64_t ffs_oracle_dispersion(const void *image, int bytes_per_pixel,
                               const uint8_t *mask, int width, int height,
                               const ffs_oracle_params *p, uint8_t *dst);
 
+/* threshold_w_gain (baseline.cpp:187-250,289-310): gain = width*height doubles. */
+int64_t ffs_oracle_dispersion_gain(const void *image, int bytes_per_pixel, const uint8_t *mask,
+                                   int width, int height, const ffs_oracle_params *p,
+                                   const double *gain, uint8_t *dst);
 int64_t ffs_oracle_dispersion_extended(const void *image, int bytes_per_pixel,
                                        const uint8_t *mask, int width, int height,
                                        const ffs_oracle_params *p, uint8_t *dst);

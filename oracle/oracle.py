@@ -73,6 +73,8 @@ def lib() -> C.CDLL:
             f = getattr(L, name)
             f.restype = C.c_int64
             f.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, u8p]
+        L.ffs_oracle_dispersion_gain.restype = C.c_int64
+        L.ffs_oracle_dispersion_gain.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, vp, u8p]
         L.ffs_oracle_extended_stage.restype = C.c_int64
         L.ffs_oracle_extended_stage.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, C.c_int, u8p]
         L.ffs_oracle_default_params.argtypes = [P]
@@ -144,6 +146,13 @@ def _threshold(fn_name: str, image, mask, params, *extra):
 
 def dispersion(image, mask, params=None) -> np.ndarray:
     return _threshold("ffs_oracle_dispersion", image, mask, params)
+
+
+def dispersion_gain(image, mask, gain, params=None) -> np.ndarray:
+    """DispersionThreshold::threshold_w_gain (baseline.cpp:187-250,289-310); gain: (H, W) float64."""
+    gain = np.ascontiguousarray(gain, dtype=np.float64)
+    assert gain.shape == image.shape
+    return _threshold("ffs_oracle_dispersion_gain", image, mask, params, gain.ctypes.data_as(C.c_void_p))
 
 
 def dispersion_extended(image, mask, params=None) -> np.ndarray:

@@ -1,0 +1,79 @@
+"""threshold_w_gain (baseline.cpp:187-250,289-310): the standard dispersion test
+with a per-pixel gain map, CUDA through the C ABI vs the CPU oracle, bit-exact."""
+import numpy as np
+import pytest
+
+from helpers import random_frame
+from ffs_b200 import synth
+from ffs_b200.spotfinder import FfsError, Spotfinder
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_mask(sf, img):
+    sf.upload(img)
+    sf.threshold(0, 1)
+    return sf.strong_mask(0)
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+@pytest.mark.parametrize("kind", ["ones", "smooth", "random"])
+def test_gain_map_matches_oracle(kind, dtype):
+    h, w = 180, 500
+    img, mask = random_frame(h, w, dtype, seed=21, lam=3.0, n_spots=25)
+    rng = np.random.default_rng(3)
+    if kind == "ones":
+        gain = np.ones((h, w))
+    elif kind == "smooth":
+        yy, xx = np.mgrid[0:h, 0:w]
+        gain = 0.6 + 1.2 * (xx / w) + 0.3 * np.sin(yy / 17.0)
+    else:
+        gain = rng.uniform(0.25, 4.0, (h, w))
+    want = oracle.dispersion_gain(img, mask, gain)
+    with Spotfinder(w, h, dtype, mask, n_slots=1) as sf:
+        plain = gpu_mask(sf, img)
+        sf.set_gain(gain)
+        got = gpu_mask(sf, img)
+        assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
+        sf.set_gain(None)  # back to the plain test
+        assert np.array_equal(gpu_mask(sf, img), plain)
+    assert np.array_equal(plain, oracle.dispersion(img, mask))
+    assert want.sum() > 0
+    if kind == "random":
+        assert (want != plain).any()
+
+
+def test_gain_with_nonpositive_entries_and_params():
+    """A non-positive gain makes sqrt(gain*x*m) NaN in the reference: those pixels fail b > d;
+    the kernel must not prune with such a map."""
+    h, w = 120, 300
+    img, mask = random_frame(h, w, np.uint16, seed=5, lam=2.0, n_spots=15)
+    gain = np.full((h, w), 1.5)
+    gain[40:60, 100:150] = 0.0
+    gain[70:80, 10:60] = -1.0
+    p = oracle.default_params(nsig_b=4.0, nsig_s=2.0, threshold=1.0)
+    want = oracle.dispersion_gain(img, mask, gain, p)
+    with Spotfinder(w, h, np.uint16, mask, n_slots=1, nsig_b=4.0, nsig_s=2.0, threshold=1.0) as sf:
+        sf.set_gain(gain)
+        got = gpu_mask(sf, img)
+    assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
+
+
+def test_gain_streaming_after_graph_capture_and_extended_rejected():
+    g = synth.small_geometry(320, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 6, np.uint16, config=6, n_spots=12)
+    gain = np.random.default_rng(1).uniform(0.5, 2.0, mask.shape)
+    with Spotfinder(g.width, g.height, np.uint16, mask, n_slots=2) as sf:
+        for i in range(4):  # slot graphs get captured without a gain map
+            sf.submit_copy(i, frames[i])
+            sf.wait()
+        sf.set_gain(gain)
+        for i in range(6):
+            sf.submit_copy(i, frames[i])
+            res, _ = sf.wait()
+            assert res.num_strong_pixels == int(oracle.dispersion_gain(frames[i], mask, gain).sum())
+    with Spotfinder(g.width, g.height, np.uint16, mask, n_slots=1, algorithm="dispersion_extended") as sf:
+        with pytest.raises(FfsError):
+            sf.set_gain(gain)

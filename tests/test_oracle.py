@@ -90,3 +90,35 @@ def test_spot_fields_and_filters():
     assert a["com_z"] == 0.5
     kept, rs, rp = oracle.filter_spots(s, 3, 2.0)
     assert (len(kept), rs, rp) == (1, 1, 0)
+
+
+def test_dispersion_gain_against_direct_window_sums():
+    """threshold_w_gain restatement (SAT, C) vs direct 7x7 integer window sums + the same fp64
+    formulas in numpy (baseline.cpp:240-246); the gain = 1 map differs from the plain test only
+    in where x*(m-1) enters (a vs c), so the two agree on ordinary data."""
+    from ffs_b200 import synth
+    g = synth.small_geometry(90, 70)
+    mask = synth.make_mask(g)
+    img = synth.make_frame(g, mask, np.uint16, 2, 3, n_spots=8, background=3.0)
+    rng = np.random.default_rng(9)
+    gain = rng.uniform(0.3, 3.0, img.shape)
+    h, w = img.shape
+    want = np.zeros((h, w), np.uint8)
+    v = img.astype(np.int64)
+    ok = (mask != 0) & (v < 2 ** 24)
+    for j in range(h):
+        for i in range(w):
+            ys, xs = slice(max(j - 3, 0), j + 4), slice(max(i - 3, 0), i + 4)
+            sel = ok[ys, xs]
+            m = float(sel.sum())
+            x = float(v[ys, xs][sel].sum())
+            y = float((v[ys, xs][sel] ** 2).sum())
+            if mask[j, i] and m >= 2 and img[j, i] > 0:
+                a = m * y - x * x
+                b = m * float(img[j, i]) - x
+                c = gain[j, i] * x * (m - 1 + 6.0 * np.sqrt(2 * (m - 1)))
+                d = 3.0 * np.sqrt(gain[j, i] * x * m)
+                want[j, i] = a > c and b > d
+    got = oracle.dispersion_gain(img, mask, gain)
+    assert np.array_equal(got, want)
+    assert np.array_equal(oracle.dispersion_gain(img, mask, np.ones(img.shape)), oracle.dispersion(img, mask))
