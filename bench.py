@@ -75,12 +75,26 @@ class CpuPath:
         self.local = threading.local()
         self.L = oracle.lib()
         self.R = oracle.ref() if self.kind == "reference" else None
+        # ONE pool for the object's lifetime: a reference context is ~0.6 GB at 16M and lives in
+        # its worker thread, so a pool per run() would leak n_threads contexts per step.
+        self.ex = ThreadPoolExecutor(max_workers=n_threads)
+        self.ctxs = []
+        self.lock = threading.Lock()
 
     def _ctx(self):
         if not hasattr(self.local, "ctx"):
             self.local.dst = np.empty((self.h, self.w), np.uint8)
             self.local.ctx = self.R.ffs_ref_create(self.w, self.h) if self.R else None
+            if self.local.ctx:
+                with self.lock:
+                    self.ctxs.append(self.local.ctx)
         return self.local.ctx, self.local.dst
+
+    def close(self):
+        self.ex.shutdown(wait=True)
+        for c in self.ctxs:
+            self.R.ffs_ref_free(c)
+        self.ctxs = []
 
     def one(self, frame):
         ctx, dst = self._ctx()
@@ -97,11 +111,12 @@ class CpuPath:
 
     def run(self, frames, n_frames):
         """Process n_frames (cycled) frame-parallel over n_threads; returns seconds."""
-        with ThreadPoolExecutor(max_workers=self.n_threads) as ex:
-            list(ex.map(self.one, [frames[i % len(frames)] for i in range(self.n_threads)]))  # warm contexts
-            t0 = time.perf_counter()
-            list(ex.map(self.one, [frames[i % len(frames)] for i in range(n_frames)]))
-            return time.perf_counter() - t0
+        ex = self.ex
+        if len(self.ctxs) < self.n_threads:  # first call: let every worker build its context
+            list(ex.map(self.one, [frames[i % len(frames)] for i in range(self.n_threads)]))
+        t0 = time.perf_counter()
+        list(ex.map(self.one, [frames[i % len(frames)] for i in range(n_frames)]))
+        return time.perf_counter() - t0
 
 
 def cpu_threads() -> int:
@@ -125,6 +140,7 @@ def run_reference_arm(args):
     for _ in range(args.warmup):
         cpu.run(frames, per_step)
     t = sum(cpu.run(frames, per_step) for _ in range(args.steps))
+    cpu.close()
     fps = per_step * args.steps / t
     sample = (f"{per_step} frames/step x {args.steps} steps, frame-parallel over {T} threads; threshold = "
               f"{'reference standalone.cc compiled in place' if cpu.kind == 'reference' else 'oracle port'}, "
@@ -390,6 +406,7 @@ def run_gpu_arm(args):
             cpu = CpuPath(mask, T)
             n = T * 2
             t = cpu.run(frames, n)
+            cpu.close()
             out["cpu_baseline"] = {"value": n / t, "unit": "frames/s", "cores": T, "kind": cpu.kind,
                                    "sample": f"{n} frames frame-parallel over {T} host threads; threshold = "
                                              f"{'reference standalone.cc (oracle/_ref)' if cpu.kind == 'reference' else 'oracle port'}"
