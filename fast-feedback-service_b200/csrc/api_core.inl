@@ -239,13 +239,10 @@ extern "C" size_t ffs_frame_bytes_device(const ffs_ctx* c) { return c ? c->frame
 extern "C" uint64_t ffs_mask_valid_count(ffs_ctx* c) { return c ? c->valid_count : 0; }
 extern "C" void ffs_free(void* p) { free(p); }
 
-// threshold_w_gain (baseline.cpp:289-310): a per-pixel gain map for the standard dispersion test.
+// threshold_w_gain: a per-pixel gain map for the standard dispersion test (baseline.cpp:289-310)
+// and for dispersion_extended (baseline.cpp:772-805).
 extern "C" int ffs_set_gain(ffs_ctx* c, const double* gain) {
     if (!c) return FFS_ERR_ARG;
-    if (c->p.algorithm != FFS_ALGO_DISPERSION) {
-        c->err = "ffs_set_gain: only the standard dispersion algorithm takes a gain map";
-        return FFS_ERR_ARG;
-    }
     FFS_CK(c, cudaSetDevice(c->p.device));
     FFS_CK(c, cudaDeviceSynchronize());
     std::lock_guard<std::mutex> lk(c->mu);
@@ -258,24 +255,28 @@ extern "C" int ffs_set_gain(ffs_ctx* c, const double* gain) {
     if (!gain) {
         cudaFree(c->d_gain);
         c->d_gain = nullptr;
-        c->gain_min = 1.0;
+        c->gain_min = c->gain_max = 1.0;
         c->gain_brute = false;
         return FFS_OK;
     }
     const size_t n = (size_t)c->p.width * c->p.height;
     std::vector<uint8_t> mask(n);
     FFS_CK(c, cudaMemcpy(mask.data(), c->d_mask, n, cudaMemcpyDeviceToHost));
-    double gmin = INFINITY;
+    double gmin = INFINITY, gmax = 0.0;
     bool bad = false;
     for (size_t k = 0; k < n; ++k) {
         if (!mask[k]) continue;
         const double g = gain[k];
         if (!(g > 0.0) || !std::isfinite(g)) bad = true;
-        else gmin = std::min(gmin, g);
+        else {
+            gmin = std::min(gmin, g);
+            gmax = std::max(gmax, g);
+        }
     }
     if (!c->d_gain) FFS_CK(c, cudaMalloc(&c->d_gain, n * sizeof(double)));
     FFS_CK(c, cudaMemcpy(c->d_gain, gain, n * sizeof(double), cudaMemcpyHostToDevice));
     c->gain_min = std::isfinite(gmin) ? gmin : 1.0;
+    c->gain_max = std::isfinite(gmin) ? gmax : 1.0;
     c->gain_brute = bad;  // sqrt of a non-positive gain: the reference yields NaN there; decide every pixel exactly
     return FFS_OK;
 }
@@ -362,6 +363,9 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     // pruning bound a lower bound
     a.sig_k = (float)(c->p.nsig_s * std::sqrt(c->d_gain ? c->gain_min : 1.0) * (1.0 - 1e-4));
     a.gain = c->d_gain;
+    // float brackets rounded outwards (the kernel's own error bound covers the table rounding)
+    a.g_lo = c->d_gain ? (float)(c->gain_min * (1.0 - 1e-6)) : 1.0f;
+    a.g_hi = c->d_gain ? (float)(c->gain_max * (1.0 + 1e-6)) : 1.0f;
     a.thr_floor = (int)std::min(std::floor(c->p.threshold), 1073741824.0);
     a.mcount = c->d_mcount;
     a.m_pitch = c->m_pitch;

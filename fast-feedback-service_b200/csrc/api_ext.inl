@@ -13,7 +13,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     a.strong_count = c->d_ext_count;
     a.chunk_count = nullptr;  // the D plane is not the connected-components input
     static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
-    if (brute) {
+    if (brute || c->gain_brute) {  // a gain map with non-positive entries cannot be bracketed
         a.force_brute = 1;
         resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
     } else {

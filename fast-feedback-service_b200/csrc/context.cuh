@@ -59,6 +59,7 @@ struct ffs_ctx {
     size_t info_pitch = 0;            // bytes per row of d_info (multiple of 16)
     double* d_gain = nullptr;         // optional gain map (ffs_set_gain), width*height
     double gain_min = 1.0;            // over the mask-valid pixels: scales the pruning bound
+    double gain_max = 1.0;            // (extended first pass: bracket of the right-hand side)
     bool gain_brute = false;          // gain map with non-positive / non-finite entries: no pruning
     uint8_t* d_mcount = nullptr;      // per pixel: valid pixels in its clipped 7x7 window (extended_stream.cuh)
     size_t m_pitch = 0;

@@ -43,6 +43,9 @@ namespace ffsb {
 #ifndef FUSED_DP2A
 #define FUSED_DP2A 1
 #endif
+#ifndef FUSED_LUT_MASK
+#define FUSED_LUT_MASK 1  // 16-bit front end: validity nibble -> {mask & clamp} words from a 16-entry shared table
+#endif
 
 template <typename PixelT>
 struct FusedGeo {
@@ -130,12 +133,28 @@ __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t
 }
 
 // ---- row front end: masked + clamped packed words, max of the masked raw values -----------
+// lut_s (16-bit pixels, FUSED_LUT_MASK): shared address of a 16-entry table, entry n = the two
+// words {0xffff per set bit of the nibble n} & {CLAMP, CLAMP}; an unsigned min against it masks
+// and clamps in one instruction.  vmax is then the max of the CLAMPED values: the caller
+// compares it with min(T, CLAMP - 1), so a group holding a pixel >= CLAMP is always a candidate
+// and a group of smaller pixels is tested as before.
 template <typename PixelT>
-__device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_t* pinfo, uint32_t (&c)[4],
-                                               uint32_t& vmax, uint32_t& info) {
+__device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_t* pinfo, uint32_t lut_s,
+                                               uint32_t (&c)[4], uint32_t& vmax, uint32_t& info) {
     constexpr uint32_t CL = FusedGeo<PixelT>::CLAMP;
     info = *reinterpret_cast<const uint16_t*>(pinfo);
-    if constexpr (sizeof(PixelT) == 2) {
+    if constexpr (sizeof(PixelT) == 2 && FUSED_LUT_MASK) {
+        const uint4 raw = ptx::lds128(pimg);
+        // the table is 128-byte aligned: (index & 0x78) | base is one LOP3
+        const uint2 ml = ptx::lds64_s(((info << 3) & 0x78u) | lut_s);
+        const uint2 mh = ptx::lds64_s(((info >> 1) & 0x78u) | lut_s);
+        c[0] = __vminu2(raw.x, ml.x);
+        c[1] = __vminu2(raw.y, ml.y);
+        c[2] = __vminu2(raw.z, mh.x);
+        c[3] = __vminu2(raw.w, mh.y);
+        const uint32_t m2 = __vmaxu2(__vimax3_u16x2(c[0], c[1], c[2]), c[3]);
+        vmax = max(m2 & 0xffffu, m2 >> 16);
+    } else if constexpr (sizeof(PixelT) == 2) {
         const uint4 raw = ptx::lds128(pimg);
         // bit k of the validity byte -> sign bit of byte k; prmt replicates sign bits to bytes
         const uint32_t zlo = (info & 0xfu) * 0x10204080u;
@@ -191,12 +210,26 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
     const int thr_floor = a.thr_floor;
     int qn = state & 0xff, pqn = (state >> 8) & 0xfff, pgn = state >> 20;
     unsigned found = 0;
-    auto resolve_full = [&](uint32_t e) {
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    // resolves one full-window pixel per active lane; 16-bit pixels whose window holds a value
+    // >= 256 are handed to the general queue (pg) -- called by converged warps only
+    auto resolve_full = [&](bool active, uint32_t e) {
         const int col = e & 0x1fff, row = e >> 13;
-        if (a.force_brute == 2) return;
-        if (resolve_pixel_full<PixelT, KH>(a, frame, col, row)) {
+        int r = 0;
+        if (active && a.force_brute != 2) {
+            if constexpr (sizeof(PixelT) == 2) r = resolve_pixel_full_small<KH>(a, frame, col, row);
+            else r = resolve_pixel_full<PixelT, KH>(a, frame, col, row) ? 1 : 0;
+        }
+        if (r == 1) {
             set_strong(a, z, col, row);
             ++found;
+        }
+        if constexpr (sizeof(PixelT) == 2) {
+            const unsigned again = __ballot_sync(0xffffffffu, r == 2);
+            if (again) {
+                if (r == 2) pg[-(pgn + __popc(again & lt_mask))] = e;
+                pgn += __popc(again);
+            }
         }
     };
     auto resolve_any = [&](uint32_t e) {
@@ -273,8 +306,9 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         __syncwarp();
         while (pqn >= 32) {
             pqn -= 32;
-            resolve_full(pq[pqn + lane]);
+            resolve_full(true, pq[pqn + lane]);
         }
+        __syncwarp();  // pixels handed over to pg above
         while (pgn >= 32) {
             pgn -= 32;
             resolve_any(pg[-(pgn + lane)]);
@@ -282,8 +316,13 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         __syncwarp();
     }
     if (flush_all) {
-        if (lane < pqn) resolve_full(pq[lane]);
-        if (lane < pgn) resolve_any(pg[-lane]);
+        resolve_full(lane < pqn, lane < pqn ? pq[lane] : 0u);
+        __syncwarp();
+        while (pgn > 0) {  // < 64: the residue plus what the line above handed over
+            const int k = min(pgn, 32);
+            pgn -= k;
+            if (lane < k) resolve_any(pg[-(pgn + lane)]);
+        }
         pqn = pgn = 0;
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
@@ -307,6 +346,15 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
     // parameter turns every field access into a generic load from the parameter window
     // (long-scoreboard latency on each call), a shared-memory copy is one LDS away.
     __shared__ ThreshArgs sa;
+    __shared__ __align__(128) uint2 mask_lut[16];
+    if (threadIdx.x < 16) {
+        constexpr uint32_t CL = G::CLAMP;
+        const uint32_t n = threadIdx.x;
+        mask_lut[n] = make_uint2(((n & 1u) ? CL : 0u) | ((n & 2u) ? CL << 16 : 0u),
+                                 ((n & 4u) ? CL : 0u) | ((n & 8u) ? CL << 16 : 0u));
+    }
+    uint32_t lut_s;  // opaque move: keeps the address in a register instead of re-deriving it per stage
+    asm volatile("mov.u32 %0, %1;" : "=r"(lut_s) : "r"(ptx::smem_u32(mask_lut)));
     for (int t = threadIdx.x; t < 128; t += WARPS * 32) rcp_tab[t] = 0.99999f / (float)max(t & 63, 1);
     for (int t = threadIdx.x; t < (int)(sizeof(ThreshArgs) / 4); t += WARPS * 32)
         reinterpret_cast<uint32_t*>(&sa)[t] = reinterpret_cast<const uint32_t*>(&a)[t];
@@ -398,7 +446,7 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
             const int u = hb * RB + uu;  // row of the stage
             uint32_t c[4], vm, info;
             fused_load_row<PixelT>(st + u * G::IMG_ROW_BYTES + pimg_off, st + pinfo_off + u * G::INFO_ROW_BYTES,
-                                   c, vm, info);
+                                   lut_s, c, vm, info);
             // V += row(i) - row(i-7); ring slot of row i = i & 7
             uint8_t* oldp = (u + 1 < SR) ? rcur + (u + 1) * G::RING_ROW_BYTES : roth;
             const uint4 old = ptx::lds128(oldp);
@@ -475,7 +523,8 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
             const float mu = (float)xmin * rcp_tab[mub[uu]];
             float sq;
             asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
-            const int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
+            int T = max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
+            if constexpr (sizeof(PixelT) == 2 && FUSED_LUT_MASK) T = min(T, (int)G::CLAMP - 1);  // vmc is clamped
             ball[uu] = __ballot_sync(0xffffffffu,
                                     out_lane && vmc[uu] > (uint32_t)T && i >= 2 * KH && out_row < row_end);
         }
@@ -490,12 +539,14 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
 #pragma unroll
         for (int uu = 0; uu < RB; ++uu) {
             const int u = hb * RB + uu;  // row of the stage
-            const bool p = (ball[uu] >> lane) & 1u;
             const int qi = qn + __popc(ball[uu] & lt_mask);
-            ptx::sts32_if(p, gq_s + 4 * qi, (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[uu] << 14));
-            ptx::sts128_if(p, hq_s + 32 * qi, Hx[uu][0], Hx[uu][1], Hx[uu][2], Hx[uu][3]);
-            ptx::sts128_if(p, hq_s + 32 * qi + 16, Hx[uu][4], Hx[uu][5], Hx[uu][6], Hx[uu][7]);
+            ptx::push_group_if(ball[uu] & (1u << lane), gq_s + 4 * qi,
+                               (uint32_t)lane | ((uint32_t)(g * SR + u - 2 * KH) << 5) | (mub[uu] << 14),
+                               hq_s + 32 * qi, Hx[uu]);
             qn += __popc(ball[uu]);
+#if FUSED_DEBUG_MODES
+            if (a.force_brute == 3) qn = 0;  // timing experiment: streaming loop + queue pushes only
+#endif
             if ((u & 1) && qn >= 32) {
                 __syncwarp();
                 do {

@@ -135,7 +135,9 @@ __device__ __forceinline__ bool resolve_final_pixel(const ThreshArgs& a, const u
     if (!(vd > a.threshold)) return false;                  // global_mask
     // double mean = (m >= 2 ? (x / m) : 0);  local_mask = src[k] >= mean + nsig_s_ * sqrt(mean)
     const double mean = m >= 2 ? __ddiv_rn((double)x, (double)m) : 0.0;
-    return vd >= __dadd_rn(mean, __dmul_rn(a.nsig_s, __dsqrt_rn(mean)));
+    // with a gain map (baseline.cpp:706-707): src[k] >= mean + nsig_s_ * std::sqrt(gain[k] * mean)
+    const double var = a.gain ? __dmul_rn(a.gain[(size_t)row * a.width + col], mean) : mean;
+    return vd >= __dadd_rn(mean, __dmul_rn(a.nsig_s, __dsqrt_rn(var)));
 }
 
 // grid (blocks, n_frames): one thread per core pixel (or per pixel if the list overflowed)

@@ -109,10 +109,14 @@ __global__ void __launch_bounds__(WARPS * 32)
     constexpr uint32_t CL = E::CLAMP;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ float2 ktab[64];  // {m, K(m) = m-1 + nsig_b*sqrt(2(m-1))}
+    // {m, K(m)*g_lo, K(m)*g_hi},  K(m) = m-1 + nsig_b*sqrt(2(m-1)).  Without a gain map g_lo = g_hi = 1;
+    // with one (baseline.cpp:536: c = gain*x*K(m)) the smallest / largest gain bracket the
+    // right-hand side and the pixels in between are decided exactly.
+    __shared__ float4 ktab[64];
     for (int t = threadIdx.x; t < 64; t += WARPS * 32) {
         const float m1 = (float)max(t - 1, 0);
-        ktab[t] = make_float2((float)t, m1 + (float)a.nsig_b * sqrtf(2.0f * m1));
+        const float k = m1 + (float)a.nsig_b * sqrtf(2.0f * m1);
+        ktab[t] = make_float4((float)t, k * a.g_lo, k * a.g_hi, 0.f);
     }
     __syncthreads();
 
@@ -283,13 +287,13 @@ __global__ void __launch_bounds__(WARPS * 32)
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const uint32_t m = ((j < 4 ? mw.x : mw.y) >> (8 * (j & 3))) & 0xffu;
-                    const float2 mk = ktab[m];
+                    const float4 mk = ktab[m];
                     const float xf = (float)Hx[j], yf = (float)Hy[j];
-                    const float t = mk.x * yf, uu = xf * xf, rhs = xf * mk.y;
+                    const float t = mk.x * yf, uu = xf * xf, rhs_lo = xf * mk.y, rhs_hi = xf * mk.z;
                     const float lhs = t - uu;
-                    const float sl = 4e-7f * (t + uu + rhs);
+                    const float sl = 4e-7f * (t + uu + rhs_hi);
                     const bool ok = ((vb >> j) & 1u) && (int)m >= a.min_count;
-                    const bool hi = (lhs - sl) > rhs, lo = (lhs + sl) > rhs;
+                    const bool hi = (lhs - sl) > rhs_hi, lo = (lhs + sl) > rhs_lo;
                     dbits |= (ok && hi) ? (1u << j) : 0u;
                     border |= (ok && lo && !hi) ? (1u << j) : 0u;
                 }

@@ -95,6 +95,13 @@ __device__ __forceinline__ uint4 lds128(const void* p) {
     return v;
 }
 
+// 8-byte shared-memory load from a 32-bit shared address
+__device__ __forceinline__ uint2 lds64_s(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+
 // One lane of a converged warp (elect.sync): ptxas recognises the single-thread region and
 // feeds UTMALDG's uniform operands directly, where `lane == 0` costs a lane-serialising loop.
 __device__ __forceinline__ bool elect_one() {
@@ -120,6 +127,22 @@ __device__ __forceinline__ void sts128_if(bool p, uint32_t addr, uint32_t x, uin
       "@q st.shared.v4.u32 [%1], {%2, %3, %4, %5};\n\t"
       "}" ::"r"((uint32_t)p),
       "r"(addr), "r"(x), "r"(y), "r"(z), "r"(w)
+      : "memory");
+}
+
+// One queue record under one predicate: 4-byte meta word + 8 window sums (32 bytes).
+__device__ __forceinline__ void push_group_if(uint32_t pbit, uint32_t a_meta, uint32_t meta, uint32_t a_sums,
+                                              const uint32_t (&h)[8]) {
+    asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "setp.ne.u32 q, %0, 0;\n\t"
+      "@q st.shared.u32 [%1], %2;\n\t"
+      "@q st.shared.v4.u32 [%3], {%4, %5, %6, %7};\n\t"
+      "@q st.shared.v4.u32 [%3+16], {%8, %9, %10, %11};\n\t"
+      "}" ::"r"(pbit),
+      "r"(a_meta), "r"(meta), "r"(a_sums), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3]), "r"(h[4]), "r"(h[5]),
+      "r"(h[6]), "r"(h[7])
       : "memory");
 }
 

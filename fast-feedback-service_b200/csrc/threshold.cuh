@@ -62,6 +62,7 @@ struct ThreshArgs {
     int n_chunks;           // connected-components compaction's first pass); NULL = do not count
     const double* gain;     // optional per-pixel gain map, width*height row-major (threshold_w_gain,
                             // baseline.cpp:187-250); NULL = the plain test
+    float g_lo, g_hi;       // extended first pass: bracket of the gain over the valid pixels (1, 1 without a map)
     const uint8_t* mcount;  // per pixel: mask-valid pixels in its image-clipped 7x7 window
     size_t m_pitch;         // (group_info_kernel); 49 <=> window inside the image and fully valid
 };
@@ -176,6 +177,16 @@ __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t
         const double b = __dsub_rn(__dmul_rn(md, vd), xd);
         const double d = __dmul_rn(a.nsig_s, __dsqrt_rn(__dmul_rn(xd, md)));
         if (!(b > d)) return false;
+    }
+    if (EXT_PASS1 && a.gain) {
+        // baseline.cpp:535-537: double a = m * y - x * x;
+        //                       double c = gain[k] * x * (m - 1 + nsig_b_ * std::sqrt(2 * (m - 1)));
+        const double g = a.gain[(size_t)row * a.width + col];
+        const double m1 = __dsub_rn(md, 1.0);
+        const double aa = __dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd));
+        const double cc = __dmul_rn(__dmul_rn(g, xd),
+                                    __dadd_rn(m1, __dmul_rn(a.nsig_b, __dsqrt_rn(__dmul_rn(2.0, m1)))));
+        return aa > cc;
     }
     // double a = m * y - x * x - x * (m - 1);  double c = x * nsig_b_ * std::sqrt(2 * (m - 1));
     const double aa = __dsub_rn(__dsub_rn(__dmul_rn(md, yd), __dmul_rn(xd, xd)),
@@ -312,6 +323,64 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
         }
     }
     return dispersion_decide(a, m, x, y, vc, col, row);
+}
+
+// resolve_pixel_full for 16-bit frames whose window holds only pixels < 256 (the common case on
+// photon-counting data).  Returns 0 = not strong, 1 = strong, 2 = "a window pixel is >= 256":
+// the caller sends that pixel through the general exact routine.
+//   * x and y = sum v^2 both by IDP.2A: with v < 256 the low bytes of a word's two halves are
+//     the pixels themselves, so d = c + lo*lo + hi*hi is one instruction; 49 * 255^2 fits 32 bits.
+//   * m = 49, so a = 49 y - x^2 - 48 x and b = 49 v - x are exact 32-bit integers; they are
+//     compared with fp32 evaluations of c = x nsig_b sqrt(96) and d = nsig_s sqrt(49 x) first and
+//     only a pixel within 1e-4 (relative) of either boundary runs the fp64 sequence of the
+//     reference (dispersion_decide).  fp32 rounding and MUFU.SQRT are below 1e-6, so a decision
+//     taken outside that band equals the fp64 one.
+template <int KH>
+__device__ __forceinline__ int resolve_pixel_full_small(const ThreshArgs& a, const uint8_t* frame, int col, int row) {
+    static_assert(KH == 3, "constants below are for the 7x7 window");
+    const int xs = col - KH;  // >= 0 here
+    const int n_chunks = (int)(a.pitch >> 4);
+    const int ch0 = xs >> 3, o = xs & 7;
+    const int ch1 = min(ch0 + 1, n_chunks - 1);  // only read when the window reaches it
+    const uint32_t win = 0x7fu << o;             // halves 0..13 of the two chunks
+    uint32_t M[7];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t zz = ((win >> (4 * k)) & 0xfu) * 0x10204080u;
+        M[2 * k] = ptx::prmt(zz, 0u, 0x9988u);
+        if (2 * k + 1 < 7) M[2 * k + 1] = ptx::prmt(zz, 0u, 0xbbaau);
+    }
+    uint32_t x = 0, y = 0, any = 0;
+#pragma unroll
+    for (int dy = -KH; dy <= KH; ++dy) {
+        const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(row + dy) * a.pitch);
+        const uint4 A = prow[ch0];
+        const uint4 B = o > 1 ? prow[ch1] : make_uint4(0, 0, 0, 0);
+        const uint32_t w[7] = {A.x, A.y, A.z, A.w, B.x, B.y, B.z};
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const uint32_t t = w[q] & M[q];
+            any |= t;
+            x = __dp2a_lo(t, 0x0101u, x);
+            y = __dp2a_lo(t, ptx::prmt(t, 0u, 0x4420u), y);  // bytes {t.b0, t.b2}: the two pixels if < 256
+        }
+    }
+    if (any & 0xff00ff00u) return 2;
+    const uint32_t vc = reinterpret_cast<const uint16_t*>(frame + (size_t)row * a.pitch)[col];
+    if (a.gain) return dispersion_decide(a, 49u, x, (unsigned long long)y, vc, col, row) ? 1 : 0;
+    if (!(49 >= a.min_count) || !((int)vc > a.thr_floor)) return 0;
+    const int ai = (int)(49u * y - x * x - 48u * x);   // |.| < 2^28
+    const int bi = (int)(49u * vc - x);
+    const float xf = (float)x;
+    const float cf = xf * ((float)a.nsig_b * 9.797959f);            // x nsig_b sqrt(2 * 48)
+    float sq;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(49.0f * xf));
+    const float df = (float)a.nsig_s * sq;                           // nsig_s sqrt(x m)
+    const float af = (float)ai, bf = (float)bi;
+    constexpr float LO = 1.0f - 1e-4f, HI = 1.0f + 1e-4f;
+    if (af < cf * LO || bf < df * LO) return 0;          // clearly fails a > c or b > d
+    if (af > cf * HI && bf > df * HI) return 1;          // clearly passes both
+    return dispersion_decide(a, 49u, x, (unsigned long long)y, vc, col, row) ? 1 : 0;
 }
 
 __device__ __forceinline__ void set_strong(const ThreshArgs& a, int z, int col, int row) {

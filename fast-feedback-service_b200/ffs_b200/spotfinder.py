@@ -238,8 +238,8 @@ class Spotfinder:
         return res, spots[:min(n.value, max_spots)]
 
     def set_gain(self, gain):
-        """Per-pixel gain map (H, W) float64 for the standard dispersion test (threshold_w_gain,
-        baseline.cpp:289-310); None removes it."""
+        """Per-pixel gain map (H, W) float64 for threshold_w_gain: standard dispersion
+        (baseline.cpp:289-310) or dispersion_extended (baseline.cpp:772-805); None removes it."""
         if gain is None:
             self._ck(self._L.ffs_set_gain(self._ctx, None), "ffs_set_gain")
             return

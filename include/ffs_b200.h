@@ -138,9 +138,13 @@ int ffs_get_mask(ffs_ctx *ctx, uint8_t *mask_out);
 /* DispersionThreshold::threshold_w_gain (baseline/spotfinder/baseline.cpp:187-250,289-310): a
  * per-pixel gain map (width*height doubles, row-major) for the standard dispersion test:
  *     a = m*y - x*x;  c = gain*x*(m - 1 + nsig_b*sqrt(2(m-1)));  d = nsig_s*sqrt(gain*x*m).
+ * With FFS_ALGO_DISPERSION_EXTENDED the map enters as in
+ * DispersionExtendedThreshold::threshold_w_gain (baseline.cpp:484-541,657-714,772-805):
+ *     first pass  a = m*y - x*x > c = gain*x*(m - 1 + nsig_b*sqrt(2(m-1)));
+ *     final pass  src >= mean + nsig_s*sqrt(gain*mean).
  * The map is copied to the device; NULL removes it.  Not reachable from any reference
  * executable (there is no gain flag), provided for the library users of baseline.h. */
-int ffs_set_gain(ffs_ctx *ctx, const double *gain); /* width*height bytes, 0/1 */
+int ffs_set_gain(ffs_ctx *ctx, const double *gain); /* width*height doubles, row-major */
 uint64_t ffs_mask_valid_count(ffs_ctx *ctx);
 
 /* ---- device-resident (slot) API: the kernels with inputs already in HBM --------------- */

@@ -147,6 +147,27 @@ static int final_test(double m, double x, double v, int mask_k, int eroded_k,
     return dispersion_mask && global_mask && local_mask;
 }
 
+/* the gain overloads of the two extended tests: compute_dispersion_threshold(table, src,
+ * mask, gain, dst) baseline.cpp:484-541 and compute_final_threshold(table, src, mask, gain,
+ * dst) :657-714 */
+static int dispersion_test_gain(double m, double x, double y, int mask_k, double g,
+                                const ffs_oracle_params *p, int min_count) {
+    if (!(mask_k && m >= min_count && x >= 0)) return 0;
+    double a = m * y - x * x;
+    double c = g * x * (m - 1 + p->nsig_b * sqrt(2 * (m - 1)));
+    return a > c;
+}
+
+static int final_test_gain(double m, double x, double v, int mask_k, int eroded_k, double g,
+                           const ffs_oracle_params *p) {
+    if (!(mask_k && m >= 0 && x >= 0)) return 0;
+    int dispersion_mask = !eroded_k;
+    int global_mask = v > p->threshold;
+    double mean = (m >= 2 ? (x / m) : 0);
+    int local_mask = v >= (mean + p->nsig_s * sqrt(g * mean));
+    return dispersion_mask && global_mask && local_mask;
+}
+
 static int check_args(const void *image, int bpp, const uint8_t *mask, int w, int h,
                       const ffs_oracle_params *p, const uint8_t *dst) {
     if (!image || !mask || !p || !dst) return -1;
@@ -289,10 +310,11 @@ static int erode_plane(const uint8_t *mask, uint8_t *plane, int width, int heigh
     return 0;
 }
 
-/* DispersionExtendedThreshold::threshold, baseline.cpp:730-761. */
+/* DispersionExtendedThreshold::threshold, baseline.cpp:730-761; with gain != NULL
+ * threshold_w_gain, :772-805 (same sequence through the gain overloads). */
 static int64_t extended_impl(const void *image, int bpp, const uint8_t *mask, int width,
                              int height, const ffs_oracle_params *p, int stop_after_stage,
-                             uint8_t *dst) {
+                             const double *gain, uint8_t *dst) {
     int rc = check_args(image, bpp, mask, width, height, p, dst);
     if (rc) return rc;
     size_t n = (size_t)width * height;
@@ -315,7 +337,8 @@ static int64_t extended_impl(const void *image, int bpp, const uint8_t *mask, in
             double m, x, y;
             sat_window(table, width, height, i, j, p->kernel_half_x, p->kernel_half_y, &m, &x,
                        &y);
-            dst[k] = (uint8_t)dispersion_test(m, x, y, src[k], mask[k] != 0, p, min_count, 0);
+            dst[k] = gain ? (uint8_t)dispersion_test_gain(m, x, y, mask[k] != 0, gain[k], p, min_count)
+                          : (uint8_t)dispersion_test(m, x, y, src[k], mask[k] != 0, p, min_count, 0);
             count += dst[k];
         }
     if (stop_after_stage == 1) goto done;
@@ -342,7 +365,8 @@ static int64_t extended_impl(const void *image, int bpp, const uint8_t *mask, in
             double m, x, y;
             sat_window(table, width, height, i, j, p->kernel_half_x + 2, p->kernel_half_y + 2,
                        &m, &x, &y);
-            dst[k] = (uint8_t)final_test(m, x, src[k], mask[k] != 0, dst[k], p);
+            dst[k] = gain ? (uint8_t)final_test_gain(m, x, src[k], mask[k] != 0, dst[k], gain[k], p)
+                          : (uint8_t)final_test(m, x, src[k], mask[k] != 0, dst[k], p);
             count += dst[k];
         }
 done:
@@ -354,14 +378,24 @@ done:
 int64_t ffs_oracle_dispersion_extended(const void *image, int bpp, const uint8_t *mask,
                                        int width, int height, const ffs_oracle_params *p,
                                        uint8_t *dst) {
-    return extended_impl(image, bpp, mask, width, height, p, 3, dst);
+    return extended_impl(image, bpp, mask, width, height, p, 3, NULL, dst);
+}
+
+/* DispersionExtendedThreshold::threshold_w_gain, baseline.cpp:772-805.  stage as in
+ * ffs_oracle_extended_stage.  PARITY UNPINNED (see the header). */
+int64_t ffs_oracle_dispersion_extended_gain(const void *image, int bpp, const uint8_t *mask,
+                                            int width, int height, const ffs_oracle_params *p,
+                                            const double *gain, int stage, uint8_t *dst) {
+    if (!gain) return -1;
+    if (stage < 1 || stage > 3) return -6;
+    return extended_impl(image, bpp, mask, width, height, p, stage, gain, dst);
 }
 
 int64_t ffs_oracle_extended_stage(const void *image, int bpp, const uint8_t *mask, int width,
                                   int height, const ffs_oracle_params *p, int stage,
                                   uint8_t *dst) {
     if (stage < 1 || stage > 3) return -6;
-    return extended_impl(image, bpp, mask, width, height, p, stage, dst);
+    return extended_impl(image, bpp, mask, width, height, p, stage, NULL, dst);
 }
 
 /* ------------------------------------------------------------------------- */

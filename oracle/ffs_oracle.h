@@ -67,6 +67,12 @@ int64_t ffs_oracle_dispersion(const void *image, int bytes_per_pixel,
 int64_t ffs_oracle_dispersion_gain(const void *image, int bytes_per_pixel, const uint8_t *mask,
                                    int width, int height, const ffs_oracle_params *p,
                                    const double *gain, uint8_t *dst);
+/* DispersionExtendedThreshold::threshold_w_gain (baseline.cpp:484-541,657-714,772-805);
+ * stage 1/2/3 as in ffs_oracle_extended_stage (3 = the final result). */
+int64_t ffs_oracle_dispersion_extended_gain(const void *image, int bytes_per_pixel,
+                                            const uint8_t *mask, int width, int height,
+                                            const ffs_oracle_params *p, const double *gain,
+                                            int stage, uint8_t *dst);
 int64_t ffs_oracle_dispersion_extended(const void *image, int bytes_per_pixel,
                                        const uint8_t *mask, int width, int height,
                                        const ffs_oracle_params *p, uint8_t *dst);

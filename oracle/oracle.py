@@ -75,6 +75,8 @@ def lib() -> C.CDLL:
             f.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, u8p]
         L.ffs_oracle_dispersion_gain.restype = C.c_int64
         L.ffs_oracle_dispersion_gain.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, vp, u8p]
+        L.ffs_oracle_dispersion_extended_gain.restype = C.c_int64
+        L.ffs_oracle_dispersion_extended_gain.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, vp, C.c_int, u8p]
         L.ffs_oracle_extended_stage.restype = C.c_int64
         L.ffs_oracle_extended_stage.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int, P, C.c_int, u8p]
         L.ffs_oracle_default_params.argtypes = [P]
@@ -157,6 +159,14 @@ def dispersion_gain(image, mask, gain, params=None) -> np.ndarray:
 
 def dispersion_extended(image, mask, params=None) -> np.ndarray:
     return _threshold("ffs_oracle_dispersion_extended", image, mask, params)
+
+
+def dispersion_extended_gain(image, mask, gain, params=None, stage: int = 3) -> np.ndarray:
+    """DispersionExtendedThreshold::threshold_w_gain (baseline.cpp:484-541,657-714,772-805)."""
+    gain = np.ascontiguousarray(gain, dtype=np.float64)
+    assert gain.shape == image.shape
+    return _threshold("ffs_oracle_dispersion_extended_gain", image, mask, params,
+                      gain.ctypes.data_as(C.c_void_p), stage)
 
 
 def extended_stage(image, mask, stage: int, params=None) -> np.ndarray:
