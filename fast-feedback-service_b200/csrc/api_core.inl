@@ -427,8 +427,10 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     if (!attr_done[c->p.device & 63]) {
         FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         // occupancy is bounded by shared memory: ask for the whole carve-out
+        // (FFS_FUSED_CARVEOUT=<percent>: developer A/B -- fewer resident warps, more L1 for stage 3's gathers)
+        static const int carve = env_int("FFS_FUSED_CARVEOUT", 0);
         FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                       cudaSharedmemCarveoutMaxShared));
+                                       carve > 0 ? carve : (int)cudaSharedmemCarveoutMaxShared));
         attr_done[c->p.device & 63] = true;
     }
     ThreshArgs a{};

@@ -547,6 +547,9 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
 #if FUSED_DEBUG_MODES
             if (a.force_brute == 3) qn = 0;  // timing experiment: streaming loop + queue pushes only
 #endif
+#if FUSED_DEBUG_MODES
+            if (a.force_brute == 3) qn = 0;  // timing experiment: streaming loop + queue pushes only
+#endif
             if ((u & 1) && qn >= 32) {
                 __syncwarp();
                 do {

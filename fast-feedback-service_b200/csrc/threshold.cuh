@@ -335,6 +335,9 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
 //     only a pixel within 1e-4 (relative) of either boundary runs the fp64 sequence of the
 //     reference (dispersion_decide).  fp32 rounding and MUFU.SQRT are below 1e-6, so a decision
 //     taken outside that band equals the fp64 one.
+__device__ __forceinline__ int full_small_decide(const ThreshArgs& a, uint32_t x, uint32_t y, uint32_t any,
+                                                 uint32_t vc, int col, int row);
+
 template <int KH>
 __device__ __forceinline__ int resolve_pixel_full_small(const ThreshArgs& a, const uint8_t* frame, int col, int row) {
     static_assert(KH == 3, "constants below are for the 7x7 window");
@@ -353,9 +356,15 @@ __device__ __forceinline__ int resolve_pixel_full_small(const ThreshArgs& a, con
     uint32_t x = 0, y = 0, any = 0;
 #pragma unroll
     for (int dy = -KH; dy <= KH; ++dy) {
+#if defined(FUSED_EXP_L1)  // timing experiment (wrong results): every gather hits the same few L1 lines
+        const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(dy + KH) * a.pitch);
+        const uint4 A = prow[ch0 & 1];
+        const uint4 B = o > 1 ? prow[ch1 & 1] : make_uint4(0, 0, 0, 0);
+#else
         const uint4* prow = reinterpret_cast<const uint4*>(frame + (size_t)(row + dy) * a.pitch);
         const uint4 A = prow[ch0];
         const uint4 B = o > 1 ? prow[ch1] : make_uint4(0, 0, 0, 0);
+#endif
         const uint32_t w[7] = {A.x, A.y, A.z, A.w, B.x, B.y, B.z};
 #pragma unroll
         for (int q = 0; q < 7; ++q) {
@@ -365,8 +374,14 @@ __device__ __forceinline__ int resolve_pixel_full_small(const ThreshArgs& a, con
             y = __dp2a_lo(t, ptx::prmt(t, 0u, 0x4420u), y);  // bytes {t.b0, t.b2}: the two pixels if < 256
         }
     }
-    if (any & 0xff00ff00u) return 2;
     const uint32_t vc = reinterpret_cast<const uint16_t*>(frame + (size_t)row * a.pitch)[col];
+    return full_small_decide(a, x, y, any, vc, col, row);
+}
+
+// The decision of resolve_pixel_full_small from the window's sums (m = 49).
+__device__ __forceinline__ int full_small_decide(const ThreshArgs& a, uint32_t x, uint32_t y, uint32_t any,
+                                                 uint32_t vc, int col, int row) {
+    if (any & 0xff00ff00u) return 2;
     if (a.gain) return dispersion_decide(a, 49u, x, (unsigned long long)y, vc, col, row) ? 1 : 0;
     if (!(49 >= a.min_count) || !((int)vc > a.thr_floor)) return 0;
     const int ai = (int)(49u * y - x * x - 48u * x);   // |.| < 2^28

@@ -81,6 +81,28 @@ def test_dispersion_sparse_background(lam, nsig_b):
     assert want.sum() > 0
 
 
+@pytest.mark.parametrize("frac", [0.002, 0.02, 0.2])
+@pytest.mark.parametrize("nsig", [(6.0, 3.0), (0.5, 0.5), (2.0, 8.0)])
+def test_dispersion_small_pixel_exact_path_and_handover(frac, nsig):
+    """16-bit full-window pixels take a 32-bit exact test when every window pixel is < 256
+    (resolve_pixel_full_small) and are handed to the general routine otherwise: sprinkle values
+    on both sides of 255/256 over a low background so that both paths, the handover queue (more
+    than a warp's worth of handovers per flush at frac = 0.2) and many near-threshold decisions
+    are exercised; all-valid mask so that the full-window path is the one taken."""
+    nsig_b, nsig_s = nsig
+    h, w = 260, 760
+    rng = np.random.default_rng(int(frac * 1000) + int(nsig_b * 10))
+    img = rng.poisson(2.0, (h, w)).astype(np.uint16)
+    hot = rng.random((h, w)) < frac
+    img[hot] = rng.choice(np.array([200, 254, 255, 256, 257, 300, 1000, 9362, 9363, 65535], np.uint16), int(hot.sum()))
+    img[100:140, 300:340] = rng.poisson(180.0, (40, 40))  # a patch whose windows stay below 256 but are not small
+    mask = np.ones((h, w), np.uint8)
+    want = oracle.dispersion(img, mask, oracle.default_params(nsig_b=nsig_b, nsig_s=nsig_s))
+    got = run_gpu(img, mask, nsig_b=nsig_b, nsig_s=nsig_s)
+    assert np.array_equal(got, want), f"{np.argwhere(got != want)[:10]}"
+    assert want.sum() > 0
+
+
 def test_dispersion_all_zero_all_masked_no_mask():
     h, w = 60, 300
     z = np.zeros((h, w), np.uint16)
