@@ -43,6 +43,9 @@ namespace ffsb {
 #ifndef FUSED_DP2A
 #define FUSED_DP2A 1
 #endif
+#ifndef FUSED_WARPS_PER_SM_16BIT
+#define FUSED_WARPS_PER_SM_16BIT 16  // register cap of the 16-bit kernel = 65536 / (32 * this); 12 for A/B builds with more rows per batch
+#endif
 #ifndef FUSED_LUT_MASK
 #define FUSED_LUT_MASK 1  // 16-bit front end: validity nibble -> {mask & clamp} words from a 16-entry shared table
 #endif
@@ -68,7 +71,7 @@ struct FusedGeo {
     // resident warps per SM the kernel is compiled for (register cap = 65536 / (32 * this)):
     // 16-bit: 4 CTAs of 4 warps at 128 registers and 13.8 KB of shared memory per warp; the
     // 32-bit front end needs more registers
-    static constexpr int MIN_WARPS_PER_SM = sizeof(PixelT) == 2 ? 16 : 12;
+    static constexpr int MIN_WARPS_PER_SM = sizeof(PixelT) == 2 ? FUSED_WARPS_PER_SM_16BIT : 12;
     static constexpr int GQ_CAP = 96;        // pending candidate groups (< 32 + 2 rows * 30)
     static constexpr int PQ_CAP = 320;       // pending candidate pixels, both kinds (< 32 + 32 + 32 * 8)
     // per queued group: 4 B meta + 32 B window sums (the centre-row pixels are re-read from the
