@@ -449,6 +449,31 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
             const long long tasks = (long long)n * a.n_strips * ((a.height + best - 1) / best);
             if (tasks >= want) break;
         }
+        // Several waves of CTAs (a batch of frames): the last, partly filled wave is idle time, so
+        // prefer the tile height whose wave count sits just below an integer, weighted by the
+        // halo rows a tile re-reads (measured on a 32-frame Eiger2 16M batch, tools/tile_sweep.sh:
+        // 12 row tiles = 2.92 waves 23.4 us/frame, 18 tiles = 4.38 waves 24.2)
+        const double slots = (double)c->sm_count * (G::MIN_WARPS_PER_SM / kWarps);
+        auto waves_of = [&](int rows) {
+            const long long t = (long long)n * a.n_strips * ((a.height + rows - 1) / rows);
+            return (double)((t + kWarps - 1) / kWarps) / slots;
+        };
+        if (waves_of(best) > 1.5) {
+            double best_score = 0.0;
+            for (int groups = 124; groups >= 16; groups -= 1) {
+                const int rows = groups * 4 - 6;
+                const double w = waves_of(rows);
+                if (w < 1.5) continue;
+                const double score = w / std::ceil(w) * rows / (rows + 6.0);
+                if (score > best_score + 1e-9) {
+                    best_score = score;
+                    best = rows;
+                }
+            }
+            // same number of row tiles, split evenly (R + 6 still a multiple of the stage depth)
+            const int tiles = (a.height + best - 1) / best;
+            best = ((a.height + tiles - 1) / tiles + 6 + 3) / 4 * 4 - 6;
+        }
         a.tile_rows = forced > 0 ? std::min(forced, 500) : best;
     }
     a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
