@@ -57,6 +57,17 @@ extern "C" int ffs_acquire(ffs_ctx* c, int* slot, void** pinned_pixels) {
     }
 }
 
+extern "C" int ffs_release(ffs_ctx* c, int slot) {
+    if (!slots_ok(c, slot, 1)) return FFS_ERR_ARG;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (c->slots[slot].state != 1) return FFS_ERR_STATE;
+        c->slots[slot].state = 0;
+    }
+    c->cv.notify_all();
+    return FFS_OK;
+}
+
 static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st);
 
 // The device work of one frame in ring slot `slot`, queued on st.  mode 0: H2D of the dense

@@ -6,6 +6,9 @@
 // available here (see DESIGN.md "Out of scope").
 #pragma once
 #include <array>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <cstdio>
 #include <filesystem>
 #include <fstream>
@@ -23,6 +26,10 @@ class Reader {
     virtual bool is_image_available(size_t index) = 0;
     // Raw compressed chunk (12-byte HDF5 bitshuffle header + body).  Empty = try again.
     virtual bool get_raw_chunk(size_t index, std::vector<uint8_t>& destination) = 0;
+    // Reads the chunk straight into caller memory (the pinned upload buffer of a ring slot).
+    // Returns the chunk size, 0 when the file is not (completely) there yet, or SIZE_MAX when
+    // it does not fit `capacity` (nothing useful is in dst then).
+    virtual size_t read_raw_chunk(size_t index, uint8_t* dst, size_t capacity) = 0;
     virtual size_t get_number_of_images() const = 0;
     virtual std::array<size_t, 2> image_shape() const = 0;  // {slow, fast}
     virtual size_t get_element_size() const = 0;
@@ -100,6 +107,27 @@ class SHMRead : public Reader {
         f.read(reinterpret_cast<char*>(dst.data()), n);
         dst.resize((size_t)f.gcount());
         return true;
+    }
+    size_t read_raw_chunk(size_t index, uint8_t* dst, size_t capacity) override {
+        const int fd = ::open(image_path(index).c_str(), O_RDONLY);
+        if (fd < 0) return 0;
+        struct stat st {};
+        if (fstat(fd, &st) != 0 || st.st_size <= 0) {
+            ::close(fd);
+            return 0;
+        }
+        if ((size_t)st.st_size > capacity) {
+            ::close(fd);
+            return SIZE_MAX;
+        }
+        size_t got = 0;
+        while (got < (size_t)st.st_size) {
+            const ssize_t r = ::read(fd, dst + got, (size_t)st.st_size - got);
+            if (r <= 0) break;
+            got += (size_t)r;
+        }
+        ::close(fd);
+        return got;
     }
     size_t get_number_of_images() const override { return num_images_; }
     std::array<size_t, 2> image_shape() const override { return shape_; }

@@ -48,6 +48,8 @@
     const size_t px = (size_t)width * height;
     std::atomic<uint32_t> next_image{0}, submitted{0}, completed{0};
     std::atomic<int> workers_alive{(int)args.threads};
+    std::atomic<bool> had_error{false};
+    std::atomic<uint32_t> failed_images{0};
     std::vector<int> thread_of(num_images, 0);
     std::mutex wait_mutex;
     double time_waiting_for_images = 0;
@@ -68,7 +70,7 @@
                     std::lock_guard<std::mutex> lk(wait_mutex);
                     if (seconds_since(last_image_received) > args.timeout) {
                         printf("Timeout waiting for image %zu\n", offset_image_num);
-                        g_stop = true;
+                        g_stop = true;  // graceful stop and exit 0, as the reference (spotfinder.cc:778-782)
                         break;
                     }
                     std::this_thread::sleep_for(100ms);
@@ -78,35 +80,48 @@
                 last_image_received = clk::now();
                 time_waiting_for_images += seconds_since(wait_start);
             }
+            int slot = -1;
+            void* pinned = nullptr;
+            if (ffs_acquire(ctx, &slot, &pinned) != FFS_OK) break;
+            thread_of[image_num] = thread_id;
+            // The compressed chunk is read straight into the slot's pinned upload buffer, uploaded
+            // and decoded on the device (bslz4_gpu.cuh).  The reference decompresses here on the
+            // host (spotfinder.cc:823-841); that path is kept for chunks the device decoder does
+            // not take (FFS_HOST_DECODE=1 forces it).
+            void* pchunk = nullptr;
+            size_t cap = 0;
+            const bool direct = !host_decode && ffs_slot_buffers(ctx, slot, nullptr, &pchunk, &cap) == FFS_OK;
+            size_t chunk_bytes = 0;
+            const uint8_t* chunk_data = nullptr;
             for (;;) {  // zero-length chunk = writer not finished: sleep and retry (:805-821)
-                if (!reader.get_raw_chunk(offset_image_num, chunk) || chunk.empty()) {
+                size_t got = direct ? reader.read_raw_chunk(offset_image_num, static_cast<uint8_t*>(pchunk), cap) : SIZE_MAX;
+                if (got == SIZE_MAX) {  // host path, or a chunk larger than the upload buffer
+                    got = reader.get_raw_chunk(offset_image_num, chunk) ? chunk.size() : 0;
+                    chunk_data = chunk.data();
+                } else {
+                    chunk_data = static_cast<const uint8_t*>(pchunk);
+                }
+                if (got == 0) {
                     printf("Race Condition?!?? Got buffer size 0 for image %u. Sleeping.\n", image_num);
                     std::this_thread::sleep_for(100ms);
                     if (g_stop) break;
                     continue;
                 }
+                chunk_bytes = got;
                 break;
             }
-            if (g_stop) break;
-            int slot = -1;
-            void* pinned = nullptr;
-            if (ffs_acquire(ctx, &slot, &pinned) != FFS_OK) break;
-            thread_of[image_num] = thread_id;
-            // The compressed chunk is uploaded and decoded on the device (bslz4_gpu.cuh).  The
-            // reference decompresses here on the host (spotfinder.cc:823-841); that path is kept
-            // for chunks the device decoder does not take (FFS_HOST_DECODE=1 forces it).
             int rc = FFS_ERR_FORMAT;
-            void* pchunk = nullptr;
-            size_t cap = 0;
-            if (!host_decode && ffs_slot_buffers(ctx, slot, nullptr, &pchunk, &cap) == FFS_OK && chunk.size() <= cap) {
-                memcpy(pchunk, chunk.data(), chunk.size());
-                rc = ffs_submit_compressed(ctx, slot, image_num, chunk.size());
+            if (chunk_bytes == 0) {  // stopped while waiting for the writer
+                ffs_release(ctx, slot);
+                break;
             }
+            if (direct && chunk_data == pchunk) rc = ffs_submit_compressed(ctx, slot, image_num, chunk_bytes);
             if (rc == FFS_ERR_FORMAT) {
                 // decompress straight into the pinned ring slot (no intermediate host copy)
-                if (bslz4::decompress_chunk(chunk.data(), chunk.size(), pinned, px, sizeof(pixel_t), scratch) != 0) {
+                if (bslz4::decompress_chunk(chunk_data, chunk_bytes, pinned, px, sizeof(pixel_t), scratch) != 0) {
                     printf("Error: could not decompress image %zu\n", offset_image_num);
                     g_stop = true;
+                    had_error = true;
                     memset(pinned, 0, px * sizeof(pixel_t));
                 }
                 rc = ffs_submit(ctx, slot, image_num);
@@ -114,6 +129,7 @@
             if (rc != FFS_OK) {
                 printf("Error: submit failed: %s\n", ffs_last_error(ctx));
                 g_stop = true;
+                had_error = true;
                 break;
             }
             submitted++;
@@ -133,13 +149,23 @@
                 continue;
             }
             if (rc != FFS_OK) {
+                // ffs_wait has already popped the slot: count it, or the exit test above never holds
                 printf("Error: %s\n", ffs_last_error(ctx));
                 g_stop = true;
+                had_error = true;
+                completed++;
                 continue;
             }
-            if (r.status == FFS_ERR_FORMAT)
+            if (r.status == FFS_ERR_FORMAT) {
+                // the device decoder rejected the chunk after the header walk accepted it: the ring
+                // slot holds a partial frame, so nothing of this image is reported
                 printf("Error: could not decompress image %llu\n", (unsigned long long)r.frame_id);
-            else if (r.status != 0)
+                had_error = true;
+                failed_images++;
+                completed++;
+                continue;
+            }
+            if (r.status != 0)
                 printf("Warning: image %llu exceeded a spot-list capacity; results truncated\n", (unsigned long long)r.frame_id);
             if (n > spots.size()) n = spots.size();
             const uint32_t image_num = (uint32_t)r.frame_id;
@@ -300,4 +326,5 @@
         printf("Total time waiting for images to appear: %.2f s\n", time_waiting_for_images);
     pipe.reset();
     ffs_destroy(ctx);
-    return 0;
+    // a run that stopped on an error must not look like a clean one to the calling service
+    return had_error ? 1 : 0;

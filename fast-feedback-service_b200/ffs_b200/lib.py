@@ -23,7 +23,7 @@ ALGO_DISPERSION = 0
 ALGO_DISPERSION_EXTENDED = 1
 
 STATUS = {0: "FFS_OK", -1: "FFS_ERR_ARG", -2: "FFS_ERR_CUDA", -3: "FFS_ERR_NO_DEVICE",
-          -4: "FFS_ERR_CAPACITY", -5: "FFS_ERR_STATE", -6: "FFS_ERR_NOMEM"}
+          -4: "FFS_ERR_CAPACITY", -5: "FFS_ERR_STATE", -6: "FFS_ERR_NOMEM", -7: "FFS_ERR_FORMAT"}
 
 
 class FfsError(RuntimeError):
@@ -108,6 +108,7 @@ SYMBOLS = {
     "ffs_get_labels": (_i, [_vp, _i, _vp]),
     "ffs_acquire": (_i, [_vp, C.POINTER(_i), C.POINTER(_vp)]),
     "ffs_submit": (_i, [_vp, _i, C.c_uint64]),
+    "ffs_release": (_i, [_vp, _i]),
     "ffs_submit_copy": (_i, [_vp, C.c_uint64, _vp]),
     "ffs_wait": (_i, [_vp, C.POINTER(FrameResult), _vp, _sz, C.POINTER(_sz)]),
     "ffs_pending": (_i, [_vp]),

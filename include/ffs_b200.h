@@ -179,6 +179,9 @@ int ffs_get_labels(ffs_ctx *ctx, int slot, int64_t *labels_out /* width*height *
  * ffs_wait blocks for the oldest submitted frame and returns its result.  Thread-safe. */
 int ffs_acquire(ffs_ctx *ctx, int *slot, void **pinned_pixels);
 int ffs_submit(ffs_ctx *ctx, int slot, uint64_t frame_id);
+/* Hand an acquired slot back without submitting it (a producer that stops while it waits
+ * for its frame, spotfinder.cc:789-791). */
+int ffs_release(ffs_ctx *ctx, int slot);
 /* Convenience: acquire + memcpy from a pageable buffer + submit. */
 int ffs_submit_copy(ffs_ctx *ctx, uint64_t frame_id, const void *pixels);
 /* spots/max_spots/n_spots as in ffs_fetch; returns FFS_ERR_STATE if nothing is pending. */
