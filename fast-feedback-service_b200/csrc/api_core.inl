@@ -101,6 +101,14 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     c->d_cand_count = c->d_strong_count + S;
     c->d_ext_count = c->d_strong_count + 2 * S;
     FFS_CK(c, cudaMemset(c->d_strong_count, 0, sizeof(unsigned) * S * 3));
+    if (p.trusted_max > 0 && (uint64_t)p.trusted_max < (p.bytes_per_pixel == 2 ? 0xffffull : 0xffffffffull)) {
+        c->trusted_on = true;
+        c->tmax = (uint32_t)p.trusted_max;
+        c->vlim = std::min<uint32_t>(c->tmax, (1u << 24) - 1u);
+        FFS_CK(c, cudaMalloc(&c->d_bad, sizeof(uint32_t) * (size_t)c->bad_cap * S));
+        FFS_CK(c, cudaMalloc(&c->d_bad_count, sizeof(unsigned) * S));
+        FFS_CK(c, cudaMemset(c->d_bad_count, 0, sizeof(unsigned) * S));
+    }
     c->cand_cap = env_int("FFS_CAND_CAP", (int)std::max<size_t>(px / 8, 4096));
     FFS_CK(c, cudaMalloc(&c->d_cand, sizeof(uint32_t) * (size_t)c->cand_cap * S));
     FFS_CK(c, cudaMalloc(&c->d_valid_count, sizeof(unsigned long long)));
@@ -201,6 +209,8 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_ext2);
     cudaFree(c->d_strong_count);
     cudaFree(c->d_cand);
+    cudaFree(c->d_bad);
+    cudaFree(c->d_bad_count);
     cudaFree(c->d_valid_count);
     for (auto& ev : c->prof_events) {
         cudaEventDestroy(ev.first);
@@ -353,7 +363,7 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.cand = c->d_cand;
     a.cand_count = c->d_cand_count;
     a.cand_cap = c->cand_cap;
-    a.force_brute = env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute;
+    a.force_brute = env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute || (c->trusted_on && c->tmax < 16384u);
     a.nsig_b = c->p.nsig_b;
     a.nsig_s = c->p.nsig_s;
     a.threshold = c->p.threshold;
@@ -371,6 +381,27 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.m_pitch = c->m_pitch;
     a.chunk_count = c->d_chunk_count;  // zeroed by threshold_impl; consumed by cc_scan_kernel
     a.n_chunks = c->n_chunks;
+    a.tmax = c->tmax;
+    a.vlim = c->vlim;
+    a.bad = c->d_bad;
+    a.bad_count = c->d_bad_count;
+    a.bad_cap = c->bad_cap;
+}
+
+// The streaming kernels list a pixel above the trusted range because its clamped value makes
+// its group / window a candidate; that needs trusted_max to sit above every clamp and group
+// threshold (9362 + 3 sqrt(9362)).  A smaller trusted_max (no real detector has one) takes the
+// exact per-pixel path.
+static bool trusted_needs_brute(const ffs_ctx* c) { return c->trusted_on && c->tmax < 16384u; }
+
+template <typename PixelT>
+static int launch_trusted_fixup(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
+    ThreshArgs a{};
+    fill_thresh_args(c, a, first_slot, n);
+    trusted_fixup_kernel<PixelT, 3><<<dim3(32, (unsigned)n), 256, 0, st>>>(a);
+    c->launches++;
+    FFS_CK(c, cudaGetLastError());
+    return FFS_OK;
 }
 
 template <typename PixelT, int PPL>
@@ -388,6 +419,7 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
     a.tile_rows = pick_tile_rows(c, n, G::OUT_COLS, kThreshSR, 3);
     a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
     a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
+    if (c->trusted_on) a.force_brute = 1;  // the round-1 prefilter knows no trusted range
     if (!a.force_brute) {
         const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
         const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
@@ -530,14 +562,19 @@ static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     FFS_CK(c, cudaMemsetAsync(c->d_cand_count + first_slot, 0, sizeof(unsigned) * n, st));
     FFS_CK(c, cudaMemsetAsync(c->d_chunk_count + (size_t)first_slot * c->n_chunks, 0,
                               sizeof(uint32_t) * c->n_chunks * n, st));
+    if (c->trusted_on) FFS_CK(c, cudaMemsetAsync(c->d_bad_count + first_slot, 0, sizeof(unsigned) * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
     static const int two_kernel = env_int("FFS_TWO_KERNEL", 0);  // A/B: the round-1 prefilter + resolve pair
-    if (two_kernel || env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute) {
+    if (two_kernel || env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute || trusted_needs_brute(c)) {
         if (c->p.bytes_per_pixel == 2) return launch_dispersion<uint16_t, 8>(c, first_slot, n, st);
         return launch_dispersion<uint32_t, 4>(c, first_slot, n, st);
     }
-    if (c->p.bytes_per_pixel == 2) return launch_fused<uint16_t>(c, first_slot, n, st);
-    return launch_fused<uint32_t>(c, first_slot, n, st);
+    int rc = c->p.bytes_per_pixel == 2 ? launch_fused<uint16_t>(c, first_slot, n, st)
+                                       : launch_fused<uint32_t>(c, first_slot, n, st);
+    // 16-bit pixels above the trusted range entered the streaming sums clamped: repair their
+    // neighbourhoods (32-bit pixels are left out of the sums by the front end itself)
+    if (rc == FFS_OK && c->trusted_on && c->p.bytes_per_pixel == 2) rc = launch_trusted_fixup<uint16_t>(c, first_slot, n, st);
+    return rc;
 }
 
 extern "C" int ffs_threshold(ffs_ctx* c, int first_slot, int n, void* stream) {

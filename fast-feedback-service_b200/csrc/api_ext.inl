@@ -13,7 +13,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     a.strong_count = c->d_ext_count;
     a.chunk_count = nullptr;  // the D plane is not the connected-components input
     static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
-    if (brute || c->gain_brute) {  // a gain map with non-positive entries cannot be bracketed
+    if (brute || c->gain_brute || trusted_needs_brute(c)) {  // a gain map with non-positive entries cannot be bracketed
         a.force_brute = 1;
         resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
     } else {
@@ -60,6 +60,11 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     // final pass over the core pixels: 11x11 window over B-valid pixels
     ThreshArgs f{};
     fill_thresh_args(c, f, first_slot, n);
+    if (c->trusted_on) {  // pixels above the trusted range are not valid background (trusted.cuh)
+        trusted_clear_kernel<PixelT><<<dim3(8, (unsigned)n), 256, 0, st>>>(f, reinterpret_cast<uint32_t*>(c->d_ext2),
+                                                                           c->bits_stride);
+        c->launches++;
+    }
     f.valid_bits = c->d_ext2;
     f.valid_frame_stride = c->bits_stride;
     final_kernel<PixelT, 5><<<dim3((unsigned)(c->sm_count * 2), (unsigned)n), 256, 0, st>>>(f, c->d_valid_bits);

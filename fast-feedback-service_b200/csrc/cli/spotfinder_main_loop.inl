@@ -8,6 +8,9 @@
     p.min_spot_size = args.min_spot_size;
     p.min_spot_size_3d = args.min_spot_size_3d;
     p.max_peak_centroid_separation = args.max_peak_centroid_separation;
+    // max_valid_pixel_value of the reference's kernels (spotfinder.cc:482,868,879): the int64 cutoff
+    // is narrowed to pixel_t at the call (spotfinder.cuh:16), reproduced here
+    p.trusted_max = (int64_t)(pixel_t)reader.get_trusted_range()[1];
     p.device = args.device;
     p.n_slots = (int32_t)std::min<uint32_t>(std::max<uint32_t>(args.threads + 2, 6), 24);
     ffs_ctx* ctx = nullptr;

@@ -72,6 +72,12 @@ struct ffs_ctx {
     unsigned int* d_ext_count = nullptr;     // alias: scratch counter of the extended first pass
     uint32_t* d_cand = nullptr;              // n_slots * cand_cap candidate pixels
     unsigned int cand_cap = 0;
+    // trusted range (trusted.cuh): mask-valid pixels above trusted_max met by the kernels
+    bool trusted_on = false;
+    uint32_t tmax = 0xffffffffu, vlim = (1u << 24) - 1u;
+    uint32_t* d_bad = nullptr;               // n_slots * bad_cap
+    unsigned int* d_bad_count = nullptr;     // n_slots
+    unsigned int bad_cap = 4096;
     unsigned long long* d_valid_count = nullptr;
     uint64_t valid_count = 0;
 

@@ -143,7 +143,7 @@ __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t
 // and a group of smaller pixels is tested as before.
 template <typename PixelT>
 __device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_t* pinfo, uint32_t lut_s,
-                                               uint32_t (&c)[4], uint32_t& vmax, uint32_t& info) {
+                                               uint32_t vlim, uint32_t (&c)[4], uint32_t& vmax, uint32_t& info) {
     constexpr uint32_t CL = FusedGeo<PixelT>::CLAMP;
     info = *reinterpret_cast<const uint16_t*>(pinfo);
     if constexpr (sizeof(PixelT) == 2 && FUSED_LUT_MASK) {
@@ -183,8 +183,9 @@ __device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_
         for (int j = 0; j < 8; ++j) {
             const uint32_t v = (info & (1u << j)) ? r[j] : 0u;
             vmax = max(vmax, v);
-            // pixels >= 2^24 are not counted by the reference (standalone.cc:90): they add 0
-            cl[j] = v < (1u << 24) ? min(v, CL) : 0u;
+            // pixels >= 2^24 are not counted by the reference (standalone.cc:90), nor are pixels
+            // above the trusted range: they add 0  (vlim = min(trusted_max, 2^24 - 1))
+            cl[j] = v <= vlim ? min(v, CL) : 0u;
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) c[k] = cl[2 * k] | (cl[2 * k + 1] << 16);
@@ -238,14 +239,20 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
     auto resolve_any = [&](uint32_t e) {
         const int col = e & 0x1fff, row = e >> 13;
         if (a.force_brute == 2) return;
-        if (resolve_pixel_wide<PixelT, KH>(a, frame, valid, col, row)) {
+        // 16-bit frames with a trusted range: the general routine leaves pixels above it out of
+        // the sums (the wide gather counts by mask bits alone)
+        const bool strong = (sizeof(PixelT) == 2 && a.vlim < 0xffffu)
+                              ? resolve_pixel<PixelT, KH, false>(a, frame, valid, col, row)
+                              : resolve_pixel_wide<PixelT, KH>(a, frame, valid, col, row);
+        if (strong) {
             set_strong(a, z, col, row);
             ++found;
         }
     };
     if (n > 0) {
-        uint32_t bits = 0, full = 0;
+        uint32_t bits = 0, full = 0, badb = 0;
         int col0 = 0, row = 0;
+        const uint32_t tmax = a.tmax;
         if (lane < n) {
             const int qi = qn - n + lane;
             const uint32_t e = gq[qi];
@@ -278,8 +285,14 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
                 asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(mu));
                 uint32_t T = (uint32_t)max(__float2int_rz(fmaf(sk, sq, mu)), thr_floor);
                 bits |= (((vb >> j) & 1u) && v[j] > T) ? (1u << j) : 0u;
+                badb |= (((vb >> j) & 1u) && v[j] > tmax) ? (1u << j) : 0u;
             }
         }
+        // Mask-valid pixels above the trusted range.  16-bit pixels reach the streaming sums
+        // clamped, not zeroed, so the bounds of the windows around such a pixel are not bounds:
+        // the pixel is listed and trusted_fixup_kernel decides its 7x7 neighbourhood exactly.
+        // (Its group always gets here: its clamped value exceeds every group threshold.)
+        for (; badb; badb &= badb - 1) note_bad_pixel(a, z, col0 + __ffs(badb) - 1, row);
         qn -= n;
         const uint32_t bf = bits & full, bg = bits & ~full;
         // one scan for both queues: fast count in the low half, general count in the high half
@@ -414,6 +427,7 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float sk = a.sig_k;             // nsig_s * (1 - 1e-4)
     const int thr_floor = a.thr_floor;
+    const uint32_t vlim = sizeof(PixelT) == 4 ? a.vlim : 0u;  // 16-bit front end does not use it (registers)
     int qn = 0;              // warp-uniform fill level of the group queue
     uint32_t pstate = 0;     // fill levels of the two pixel queues (<< 8, << 20)
     uint8_t* qbase = reinterpret_cast<uint8_t*>(gq);
@@ -449,7 +463,7 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
             const int u = hb * RB + uu;  // row of the stage
             uint32_t c[4], vm, info;
             fused_load_row<PixelT>(st + u * G::IMG_ROW_BYTES + pimg_off, st + pinfo_off + u * G::INFO_ROW_BYTES,
-                                   lut_s, c, vm, info);
+                                   lut_s, vlim, c, vm, info);
             // V += row(i) - row(i-7); ring slot of row i = i & 7
             uint8_t* oldp = (u + 1 < SR) ? rcur + (u + 1) * G::RING_ROW_BYTES : roth;
             const uint4 old = ptx::lds128(oldp);

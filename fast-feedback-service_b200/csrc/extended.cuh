@@ -124,14 +124,16 @@ __device__ __forceinline__ bool resolve_final_pixel(const ThreshArgs& a, const u
             const int xx = x0 + k;
             if (xx <= x1) {
                 const uint32_t pv = prow[xx];
-                if (((bits >> k) & 1u) && pv < (1u << 24)) {
+                if (((bits >> k) & 1u) && pv <= a.vlim) {
                     m += 1;
                     x += pv;
                 }
             }
         }
     }
-    const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    if (vc > a.tmax) return false;                          // above the trusted range: mask'[k] is false
+    const double vd = (double)vc;
     if (!(vd > a.threshold)) return false;                  // global_mask
     // double mean = (m >= 2 ? (x / m) : 0);  local_mask = src[k] >= mean + nsig_s_ * sqrt(mean)
     const double mean = m >= 2 ? __ddiv_rn((double)x, (double)m) : 0.0;

@@ -55,6 +55,11 @@ __device__ __noinline__ uint32_t ext_resolve(const ThreshArgs* __restrict__ ap, 
     unsigned found = 0;
     auto resolve_entry = [&](uint32_t e) {
         const int col = e & 0x1fff, row = e >> 13;
+        if (a.tmax != 0xffffffffu) {  // a mask-valid centre above the trusted range (trusted.cuh)
+            const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+            if (vc > a.tmax && ((a.valid_bits[(size_t)row * a.valid_pitch + (col >> 3)] >> (col & 7)) & 1u))
+                note_bad_pixel(a, z, col, row);
+        }
         if (resolve_pixel<PixelT, 3, true>(a, frame, a.valid_bits, col, row)) {
             set_strong(a, z, col, row);
             ++found;

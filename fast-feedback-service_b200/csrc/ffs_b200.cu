@@ -6,6 +6,7 @@
 #include "dispersion_fused.cuh"
 #include "extended_stream.cuh"
 #include "extended.cuh"
+#include "trusted.cuh"
 #include "cc.cuh"
 #include "cc3d.cuh"
 #include "bslz4_gpu.cuh"

@@ -65,7 +65,21 @@ struct ThreshArgs {
     float g_lo, g_hi;       // extended first pass: bracket of the gain over the valid pixels (1, 1 without a map)
     const uint8_t* mcount;  // per pixel: mask-valid pixels in its image-clipped 7x7 window
     size_t m_pitch;         // (group_info_kernel); 49 <=> window inside the image and fully valid
+    // Trusted range (reader.get_trusted_range()[1], spotfinder.cc:482,868,879): a pixel
+    // above trusted_max is treated exactly like a masked one -- never strong, never in a window sum.
+    uint32_t tmax;          // a centre pixel above this is invalid (0xffffffff = no trusted range)
+    uint32_t vlim;          // a window pixel is counted iff v <= vlim = min(tmax, 2^24 - 1)  (standalone.cc:90)
+    uint32_t* bad;          // per slot: bad_cap entries col | row << 13 of mask-valid pixels above tmax,
+    unsigned int* bad_count;  // appended by whoever meets one as a centre pixel (may run past bad_cap)
+    unsigned int bad_cap;
 };
+
+// A mask-valid centre pixel above the trusted maximum: remember it for trusted_fixup_kernel.
+__device__ __forceinline__ void note_bad_pixel(const ThreshArgs& a, int z, int col, int row) {
+    if (!a.bad_count) return;
+    const unsigned k = atomicAdd(a.bad_count + z, 1u);
+    if (k < a.bad_cap) a.bad[(size_t)z * a.bad_cap + k] = (uint32_t)col | ((uint32_t)row << 13);
+}
 
 template <typename PixelT, int KH_, int PPL_, int SR_>
 struct ThreshGeo {
@@ -109,6 +123,7 @@ struct ThreshGeo {
 __device__ __forceinline__ bool dispersion_decide(const ThreshArgs& a, uint32_t m, uint32_t x,
                                                   unsigned long long y, uint32_t v, int col, int row) {
     const double vd = (double)v, md = (double)m, xd = (double)x, yd = (double)y;
+    if (v > a.tmax) return false;  // above the trusted range: an invalid pixel
     if (!((int)m >= a.min_count)) return false;
     if (!(vd > a.threshold)) return false;
     const double b = __dsub_rn(__dmul_rn(md, vd), xd);
@@ -156,7 +171,7 @@ __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t
             if (xx <= x1) {
                 const uint32_t pv = prow[xx];
                 // int mm = (mask[k] && src[k] < BIG) ? 1 : 0;   standalone.cc:90
-                if (((bits >> k) & 1u) && pv < (1u << 24)) {
+                if (((bits >> k) & 1u) && pv <= a.vlim) {
                     m += 1;
                     x += pv;
                     y += (unsigned long long)pv * pv;
@@ -167,7 +182,9 @@ __device__ __forceinline__ bool resolve_pixel(const ThreshArgs& a, const uint8_t
     if (!EXT_PASS1)
         return dispersion_decide(a, m, x, y, (uint32_t) reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col],
                                  col, row);
-    const double vd = (double)reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+    if (vc > a.tmax) return false;  // above the trusted range: an invalid pixel (the caller notes it)
+    const double vd = (double)vc;
     const double md = (double)m, xd = (double)x, yd = (double)y;
     // if (mask[k] && m >= min_count_ && x >= 0 && src[k] > threshold_)
     if (!((int)m >= a.min_count)) return false;
@@ -239,6 +256,7 @@ __device__ __forceinline__ bool resolve_pixel_wide(const ThreshArgs& a, const ui
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 if constexpr (sizeof(PixelT) == 2) {
+                    // (16-bit data with a trusted range goes through resolve_pixel instead: see resolve_any)
                     const uint32_t lo = (sel >> (k * 8 + 2 * q)) & 1u ? (wv[q] & 0xffffu) : 0u;
                     const uint32_t hi = (sel >> (k * 8 + 2 * q + 1)) & 1u ? (wv[q] >> 16) : 0u;
                     x += lo + hi;
@@ -246,7 +264,7 @@ __device__ __forceinline__ bool resolve_pixel_wide(const ThreshArgs& a, const ui
                     y += (unsigned long long)hi * hi;
                 } else {
                     // int mm = (mask[k] && src[k] < BIG) ? 1 : 0;   standalone.cc:90
-                    const bool counted = ((sel >> (k * 4 + q)) & 1u) && wv[q] < (1u << 24);
+                    const bool counted = ((sel >> (k * 4 + q)) & 1u) && wv[q] <= a.vlim;
                     const uint32_t pv = counted ? wv[q] : 0u;
                     m += counted ? 1u : 0u;
                     x += pv;
@@ -314,7 +332,7 @@ __device__ __forceinline__ bool resolve_pixel_full(const ThreshArgs& a, const ui
             for (int q = 0; q < 10; ++q) {
                 // int mm = (mask[k] && src[k] < BIG) ? 1 : 0;   standalone.cc:90
                 const bool in = (win >> q) & 1u;
-                const bool counted = in && w[q] < (1u << 24);
+                const bool counted = in && w[q] <= a.vlim;
                 const uint32_t pv = counted ? w[q] : 0u;
                 m -= (in && !counted) ? 1u : 0u;
                 x += pv;
@@ -430,6 +448,11 @@ __global__ void __launch_bounds__(256) resolve_kernel(const ThreshArgs a) {
             const uint32_t e = list[t];
             col = e & 0x1fff;
             row = e >> 13;
+        }
+        if (EXT_PASS1 && a.tmax != 0xffffffffu) {  // extended: trusted_clear_kernel needs the list (trusted.cuh)
+            const uint32_t vc = reinterpret_cast<const PixelT*>(frame + (size_t)row * a.pitch)[col];
+            if (vc > a.tmax && ((valid[(size_t)row * a.valid_pitch + (col >> 3)] >> (col & 7)) & 1u))
+                note_bad_pixel(a, z, col, row);
         }
         if (resolve_pixel<PixelT, KH, EXT_PASS1>(a, frame, valid, col, row)) {
             set_strong(a, z, col, row);

@@ -41,6 +41,7 @@ class Params(C.Structure):
         ("max_peak_centroid_separation", C.c_float),
         ("cc_row_wrap", C.c_int32), ("device", C.c_int32), ("n_slots", C.c_int32),
         ("max_strong_per_frame", C.c_uint32), ("max_spots_per_frame", C.c_uint32),
+        ("trusted_max", C.c_int64),
     ]
 
 

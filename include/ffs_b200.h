@@ -81,6 +81,13 @@ typedef struct ffs_params {
     int32_t n_slots;          /* frames resident on the device at once (batch / ring depth)     */
     uint32_t max_strong_per_frame; /* capacity of the per-frame strong-pixel list (0 = default) */
     uint32_t max_spots_per_frame;  /* capacity of the per-frame spot list         (0 = default) */
+    int64_t trusted_max;      /* upper end of the trusted range, reader.get_trusted_range()[1] as
+                                 spotfinder.cc:482,868,879 passes it to the kernels
+                                 (max_valid_pixel_value); <= 0 = none.  A mask-valid pixel ABOVE
+                                 it is treated exactly like a masked pixel: never strong
+                                 (thresholding.cu:208-209) and -- unlike the reference GPU
+                                 kernel, like the CPU algorithm run on mask && v <= trusted_max --
+                                 not part of any window sum either.             */
 } ffs_params;
 
 /* One connected component.  Mirrors Reflection3D (connected_components.hpp:31-268):

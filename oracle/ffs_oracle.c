@@ -310,6 +310,16 @@ static int erode_plane(const uint8_t *mask, uint8_t *plane, int width, int heigh
     return 0;
 }
 
+/* Exported for the independent cross-checks in tests/test_oracle.py
+ * (scipy.ndimage.distance_transform_cdt(metric="chessboard") and a direct 5x5 predicate). */
+void ffs_oracle_chebyshev_to_zero(const uint8_t *plane, int width, int height, int32_t *dist) {
+    chebyshev_to_zero(plane, width, height, (int *)dist);
+}
+int ffs_oracle_erode(const uint8_t *mask, uint8_t *plane, int width, int height,
+                     const ffs_oracle_params *p) {
+    return erode_plane(mask, plane, width, height, p);
+}
+
 /* DispersionExtendedThreshold::threshold, baseline.cpp:730-761; with gain != NULL
  * threshold_w_gain, :772-805 (same sequence through the gain overloads). */
 static int64_t extended_impl(const void *image, int bpp, const uint8_t *mask, int width,

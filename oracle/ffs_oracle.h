@@ -94,6 +94,13 @@ int64_t ffs_oracle_dispersion_extended_bruteforce(const void *image, int bytes_p
                                                   int height, const ffs_oracle_params *p,
                                                   uint8_t *dst);
 
+/* chebyshev_distance(src, false, dst) as restated from DIALS (call site baseline.cpp:558) and
+ * erode_dispersion_mask (baseline.cpp:552-571), exported so tests can cross-check them against
+ * independent implementations. */
+void ffs_oracle_chebyshev_to_zero(const uint8_t *plane, int width, int height, int32_t *dist);
+int ffs_oracle_erode(const uint8_t *mask, uint8_t *plane_inout, int width, int height,
+                     const ffs_oracle_params *p);
+
 /* Resolution mask (kernels/masking.cu:37-147), applied in place to a u8 mask. */
 void ffs_oracle_resolution_mask(uint8_t *mask, int width, int height, float wavelength,
                                 float distance_m, float beam_center_x_px,

@@ -82,6 +82,10 @@ def lib() -> C.CDLL:
         L.ffs_oracle_default_params.argtypes = [P]
         L.ffs_oracle_resolution_mask.restype = None
         L.ffs_oracle_resolution_mask.argtypes = [u8p, C.c_int, C.c_int] + [C.c_float] * 8
+        L.ffs_oracle_chebyshev_to_zero.restype = None
+        L.ffs_oracle_chebyshev_to_zero.argtypes = [u8p, C.c_int, C.c_int, vp]
+        L.ffs_oracle_erode.restype = C.c_int
+        L.ffs_oracle_erode.argtypes = [u8p, u8p, C.c_int, C.c_int, P]
         L.ffs_oracle_connected_components.restype = C.c_int64
         L.ffs_oracle_connected_components.argtypes = [u8p, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                                       i64p, vp, C.c_int64]
@@ -114,6 +118,73 @@ def ref() -> C.CDLL:
                                          C.c_size_t, C.c_int, C.c_void_p]
         _REF = R
     return _REF
+
+
+_REFGPU = {}
+
+
+def refgpu_available(bytes_per_pixel: int = 2) -> bool:
+    return (_HERE / ("_ref/libffs_refgpu.so" if bytes_per_pixel == 2 else "_ref/libffs_refgpu32.so")).exists()
+
+
+def refgpu(bytes_per_pixel: int = 2) -> C.CDLL:
+    """The reference's own CUDA kernels (spotfinder/spotfinder.cu, kernels/*.cu) compiled in place
+    for sm_100 behind oracle/refgpu_shim.cu: the "kernel to beat" and the resolution-mask pin."""
+    if bytes_per_pixel not in _REFGPU:
+        name = "_ref/libffs_refgpu.so" if bytes_per_pixel == 2 else "_ref/libffs_refgpu32.so"
+        G = C.CDLL(str(_HERE / name))
+        G.ffs_refgpu_last_error.restype = C.c_char_p
+        G.ffs_refgpu_run.restype = C.c_int
+        G.ffs_refgpu_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                     C.c_float, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_double)]
+        G.ffs_refgpu_run_kernels.restype = C.c_int
+        G.ffs_refgpu_run_kernels.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_float, C.c_float, C.c_double, C.c_int, C.POINTER(C.c_double)]
+        G.ffs_refgpu_resolution_mask.restype = C.c_int
+        G.ffs_refgpu_resolution_mask.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_float] * 8
+        assert G.ffs_refgpu_bytes_per_pixel() == bytes_per_pixel
+        _REFGPU[bytes_per_pixel] = G
+    return _REFGPU[bytes_per_pixel]
+
+
+def refgpu_run(frames, mask, algorithm=ALGO_DISPERSION, min_count=3, nsig_b=6.0, nsig_s=3.0, max_valid=None,
+               repeats=1, want_strong=True, kernels_only=False):
+    """Run the reference GPU wrappers (call_do_spotfinding_dispersion/_extended,
+    spotfinder/spotfinder.cuh:9-34; defaults min_count=3, 6, 3 as declared there) over
+    frames (N, H, W).  Returns (strong (N,H,W) u8 | None, ms for `repeats` passes over all N)."""
+    frames = np.ascontiguousarray(frames)
+    if frames.ndim == 2:
+        frames = frames[None]
+    n, h, w = frames.shape
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    G = refgpu(frames.dtype.itemsize)
+    if max_valid is None:
+        max_valid = float(np.iinfo(frames.dtype).max)
+    ms = C.c_double(0)
+    if kernels_only:
+        rc = G.ffs_refgpu_run_kernels(frames.ctypes.data, mask.ctypes.data, w, h, n, algorithm, min_count, nsig_b,
+                                      nsig_s, max_valid, repeats, C.byref(ms))
+        strong = None
+    else:
+        strong = np.empty((n, h, w), np.uint8) if want_strong else None
+        rc = G.ffs_refgpu_run(frames.ctypes.data, mask.ctypes.data, w, h, n, algorithm, min_count, nsig_b, nsig_s,
+                              max_valid, repeats, strong.ctypes.data if want_strong else None, C.byref(ms))
+    if rc:
+        raise RuntimeError(f"refgpu: {G.ffs_refgpu_last_error().decode()} ({rc})")
+    return strong, ms.value
+
+
+def refgpu_resolution_mask(mask, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m, dmin, dmax) -> np.ndarray:
+    """apply_resolution_filtering (spotfinder.cc:110-137) = the reference's apply_resolution_mask
+    kernel itself (kernels/masking.cu:99-147), run on the GPU."""
+    out = np.ascontiguousarray(mask, dtype=np.uint8).copy()
+    h, w = out.shape
+    G = refgpu(2)
+    rc = G.ffs_refgpu_resolution_mask(out.ctypes.data, w, h, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m,
+                                      dmin, dmax)
+    if rc:
+        raise RuntimeError(f"refgpu: {G.ffs_refgpu_last_error().decode()} ({rc})")
+    return out
 
 
 def default_params(**kw) -> OracleParams:
@@ -201,6 +272,36 @@ def resolution_mask(mask, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m, 
     lib().ffs_oracle_resolution_mask(out.ctypes.data, w, h, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m,
                                      dmin, dmax)
     return out
+
+
+def chebyshev_to_zero(plane) -> np.ndarray:
+    """The oracle's restatement of dials chebyshev_distance(src, false, dst) (baseline.cpp:558)."""
+    plane = np.ascontiguousarray(plane, dtype=np.uint8)
+    h, w = plane.shape
+    dist = np.empty((h, w), np.int32)
+    lib().ffs_oracle_chebyshev_to_zero(plane.ctypes.data, w, h, dist.ctypes.data)
+    return dist
+
+
+def erode(mask, plane, params=None) -> np.ndarray:
+    """erode_dispersion_mask (baseline.cpp:552-571): 1 = valid pixel outside the eroded signal core."""
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    out = np.ascontiguousarray(plane, dtype=np.uint8).copy()
+    h, w = out.shape
+    p = params or default_params()
+    rc = lib().ffs_oracle_erode(mask.ctypes.data, out.ctypes.data, w, h, C.byref(p))
+    if rc:
+        raise ValueError(f"erode failed: {rc}")
+    return out
+
+
+def format_reflections_3d(spots) -> list[str]:
+    """The lines of 3d_reflections.txt as the reference writes them (spotfinder.cc:1119-1148:
+    ostream << with the default 6 significant digits for the float centre of mass; golden
+    sample tests/3d_connected_components.sh:55-64)."""
+    return [f"X: [{int(s['x_min'])}, {int(s['x_max'])}] Y: [{int(s['y_min'])}, {int(s['y_max'])}] "
+            f"Z: [{int(s['z_min'])}, {int(s['z_max'])}] "
+            f"COM: ({float(s['com_x']):g}, {float(s['com_y']):g}, {float(s['com_z']):g})" for s in spots]
 
 
 def connected_components(strong, image, row_wrap=True, want_labels=True):

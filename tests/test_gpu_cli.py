@@ -77,6 +77,30 @@ def test_stills_json_lines_and_stdout(tmp_path, host_decode):
     assert re.search(r"\n5 images in [\d.]+ s \([\d.]+ GBps\) \([\d.]+ fps\)", out)
 
 
+def test_trusted_range_from_the_stream_header(tmp_path):
+    """countrate_correction_count_cutoff -> get_trusted_range()[1] -> the kernels
+    (spotfinder.cc:482,868,879): unmasked pixels above it are invalid."""
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 3, np.uint16, config=8, n_spots=12)
+    rng = np.random.default_rng(4)
+    for f in frames:
+        f[rng.integers(0, 200, 12), rng.integers(0, 300, 12)] = 60001 + rng.integers(0, 5000, 12)
+    write_stream(tmp_path, frames, mask, 16)  # cutoff 60000
+    rc, lines, out, err = run("spotfinder", [str(tmp_path), "--threads", "2"])
+    assert rc == 0 and err == ""
+    changed = 0
+    for l in lines:
+        f = frames[l["file-number"]]
+        folded = (mask.astype(bool) & (f <= 60000)).astype(np.uint8)
+        want = oracle.dispersion(f, folded)
+        changed += int(want.sum()) != int(oracle.dispersion(f, mask).sum())
+        _, spots = oracle.connected_components(want, f, want_labels=False)
+        assert l["num_strong_pixels"] == int(want.sum())
+        assert l["n_spots_total"] == int((spots["num_pixels"] >= 3).sum())
+    assert len(lines) == 3 and changed > 0
+
+
 def test_bit_depth_exit_code_and_spotfinder32(tmp_path):
     g = synth.small_geometry(200, 150)
     mask = synth.make_mask(g)

@@ -8,6 +8,7 @@ import pytest
 from scipy import ndimage
 
 from helpers import random_frame, unpack_bits
+from ffs_b200 import synth
 from oracle import oracle
 
 GOLDEN = np.load(Path(__file__).parent / "golden" / "dispersion_ref.npz")
@@ -168,3 +169,84 @@ def test_extended_gain_against_direct_window_sums():
     # a unit gain map and the plain algorithm agree on ordinary data (they differ only in rounding)
     assert np.array_equal(oracle.dispersion_extended_gain(img, mask, np.ones(img.shape)),
                           oracle.dispersion_extended(img, mask))
+
+
+def test_chebyshev_restatement_vs_scipy_and_direct_predicate():
+    """dials::algorithms::chebyshev_distance is un-vendored (DIALS 3.25, call site
+    baseline.cpp:558).  Two independent stand-ins pin the restatement: scipy's chessboard
+    chamfer transform (an unrelated implementation of the same published algorithm) wherever
+    the plane holds a zero, and the only thing the caller consumes -- `distance >= 3`
+    (baseline.cpp:561,566) -- against a direct in-image 5x5 "no zero pixel" test."""
+    rng = np.random.default_rng(42)
+    for h, w, density in [(40, 57, 0.5), (64, 64, 0.9), (33, 120, 0.97), (7, 9, 0.8), (1, 30, 0.7), (30, 1, 0.7)]:
+        plane = (rng.random((h, w)) < density).astype(np.uint8)
+        plane[rng.integers(0, h), rng.integers(0, w)] = 0  # at least one zero: scipy's transform is defined
+        got = oracle.chebyshev_to_zero(plane)
+        want = ndimage.distance_transform_cdt(plane, metric="chessboard")
+        assert np.array_equal(got, want.astype(np.int32)), (h, w)
+        # the predicate the erosion uses: no zero within L-infinity distance 2 inside the image
+        pad = np.pad(plane, 2, constant_values=1)  # out-of-image = far (not zero)
+        no_zero_5x5 = np.ones((h, w), bool)
+        for dy in range(5):
+            for dx in range(5):
+                no_zero_5x5 &= pad[dy:dy + h, dx:dx + w] != 0
+        assert np.array_equal(got >= 3, no_zero_5x5)
+    # a plane without any zero: everything is "far"
+    assert (oracle.chebyshev_to_zero(np.ones((12, 17), np.uint8)) >= 3).all()
+
+
+def test_erosion_restatement_against_binary_erosion():
+    """erode_dispersion_mask (baseline.cpp:552-571): `dst = mask ? !(dst && distance >= 3) : false`.
+    The kept core (dst && distance >= 3) is a morphological erosion of the first-pass plane by a
+    5x5 square with out-of-image treated as set -- scipy.ndimage.binary_erosion(border_value=1)."""
+    rng = np.random.default_rng(7)
+    for seed in range(4):
+        h, w = 50 + 7 * seed, 80 + 13 * seed
+        img, mask = random_frame(h, w, np.uint16, seed=seed, lam=1.0, n_spots=25)
+        s1 = oracle.extended_stage(img, mask, 1)  # first pass: 1 = a > c (never set on masked pixels)
+        core = ndimage.binary_erosion(s1.astype(bool), structure=np.ones((5, 5), bool), border_value=1)
+        want = np.where(mask != 0, ~core, False).astype(np.uint8)
+        assert np.array_equal(oracle.erode(mask, s1), want)
+        assert np.array_equal(oracle.extended_stage(img, mask, 2), want)
+    # dense random planes exercise every neighbourhood shape
+    plane = (rng.random((70, 90)) < 0.93).astype(np.uint8)
+    mask = (rng.random((70, 90)) < 0.95).astype(np.uint8)
+    plane &= mask
+    core = ndimage.binary_erosion(plane.astype(bool), structure=np.ones((5, 5), bool), border_value=1)
+    assert np.array_equal(oracle.erode(mask, plane), np.where(mask != 0, ~core, False).astype(np.uint8))
+
+
+def test_3d_reflections_text_format_and_order():
+    """The reference publishes 3D reflections as text (spotfinder.cc:1119-1148); its own test holds
+    ten golden lines (tests/3d_connected_components.sh:55-64).  The data set is not available
+    offline, so what is pinned here is the line format those goldens have and the order the
+    CURRENT code produces: reflections_3d[label] with boost labels in ascending lowest vertex
+    id, vertices numbered slice by slice in ascending linear index (connected_components.cc:
+    292-309,396-399), i.e. ascending minimum (z, index), then stable filters (:207-236).
+    (The golden file lists descending y: it predates the indexed `reflections_3d[label]` store --
+    the unused `label_to_vertices` unordered_map at :400-405 is what used to be iterated.)"""
+    import re
+    golden = ["X: [1896, 1899] Y: [3012, 3015] Z: [2, 4] COM: (1897.64, 3014.76, 3.3673)",
+              "X: [1388, 1390] Y: [2599, 2601] Z: [0, 4] COM: (1389.43, 2600.66, 2)"]
+    pat = re.compile(r"^X: \[\d+, \d+\] Y: \[\d+, \d+\] Z: \[\d+, \d+\] COM: \([0-9.e+]+, [0-9.e+]+, [0-9.e+]+\)$")
+    assert all(pat.match(g) for g in golden)
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    sweep = synth.make_sweep(g, mask, 8, np.uint16, n_reflections=40)
+    strong = np.stack([oracle.dispersion(f, mask) for f in sweep])
+    _, spots = oracle.connected_components(strong, sweep, row_wrap=True, want_labels=False)
+    kept, _, _ = oracle.filter_spots(spots, 3, 2.0)
+    lines = oracle.format_reflections_3d(kept)
+    assert len(lines) >= 10 and all(pat.match(l) for l in lines)
+    # order: ascending minimum (z, linear index) survives the stable filters
+    lab = kept["label"].astype(np.int64)
+    assert np.all(np.diff(lab) > 0)
+    px = g.width * g.height
+    assert np.all((lab // px) == kept["z_min"])  # the label's slice is the component's first slice
+    # a known component: two pixels in consecutive slices at the same index
+    s = np.zeros((3, 4, 5), np.uint8)
+    im = np.zeros((3, 4, 5), np.uint16)
+    s[0, 1, 2] = s[1, 1, 2] = 1
+    im[0, 1, 2], im[1, 1, 2] = 30, 10
+    _, sp = oracle.connected_components(s, im, want_labels=False)
+    assert oracle.format_reflections_3d(sp) == ["X: [2, 2] Y: [1, 1] Z: [0, 1] COM: (2.5, 1.5, 0.75)"]

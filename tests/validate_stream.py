@@ -61,7 +61,10 @@ def main() -> int:
         for i in range(n):
             frame = decompress_chunk((d / f"image_{i:06d}_2").read_bytes(), dtype, h * w).reshape(h, w)
             fn = oracle.dispersion if a.algorithm == "dispersion" else oracle.dispersion_extended
-            yy, xx = np.nonzero(fn(frame, mask))
+            # trusted range: pixels above the (pixel_t-narrowed) count cutoff are invalid
+            cutoff = int(np.array(int(hdr.get("countrate_correction_count_cutoff", 0))).astype(dtype))
+            m = mask & (frame <= cutoff) if cutoff > 0 else mask
+            yy, xx = np.nonzero(fn(frame, m.astype(np.uint8)))
             want = "".join(f"{x:4d}, {y:4d}\n" for x, y in zip(xx, yy))
             got = (Path(tmp) / f"pixels_{i:05d}.txt").read_text()
             ok = got == want
