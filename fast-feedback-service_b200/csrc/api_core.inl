@@ -78,7 +78,13 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     }
     c->sm_count = prop.multiProcessorCount;
     const size_t px = (size_t)p.width * p.height;
-    c->pitch = round_up((size_t)p.width * p.bytes_per_pixel, 128);
+    // TMA needs 16-byte-aligned row strides.  A row that already is (32-bit Eiger2 16M, Jungfrau)
+    // keeps the dense layout, so a frame arrives with one contiguous copy and nothing else;
+    // otherwise rows are padded (to 128 bytes) and the streaming path re-pitches on the device.
+    {
+        const size_t row = (size_t)p.width * p.bytes_per_pixel;
+        c->pitch = (row % 16 == 0 && !env_int("FFS_PITCH128", 0)) ? row : round_up(row, 128);
+    }
     c->frame_stride = c->pitch * p.height;
     c->bits_pitch = round_up((p.width + 7) / 8, 16);
     c->bits_stride = round_up(c->bits_pitch * p.height, 256);
@@ -404,6 +410,21 @@ static int launch_trusted_fixup(ffs_ctx* c, int first_slot, int n, cudaStream_t 
     return FFS_OK;
 }
 
+// ffs_profile_*: the next event pair that brackets the threshold kernel(s) of one launch
+static void prof_pair(ffs_ctx* c, cudaEvent_t& e0, cudaEvent_t& e1) {
+    if (!c->prof_on) return;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (c->prof_used == c->prof_events.size()) {
+        std::pair<cudaEvent_t, cudaEvent_t> ev;
+        cudaEventCreate(&ev.first);
+        cudaEventCreate(&ev.second);
+        c->prof_events.push_back(ev);
+    }
+    e0 = c->prof_events[c->prof_used].first;
+    e1 = c->prof_events[c->prof_used].second;
+    c->prof_used++;
+}
+
 template <typename PixelT, int PPL>
 static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     using G = ThreshGeo<PixelT, 3, PPL, kThreshSR>;
@@ -424,18 +445,7 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
         const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
         const unsigned grid = (unsigned)((tasks + kThreshWarps - 1) / kThreshWarps);
         cudaEvent_t e0 = nullptr, e1 = nullptr;
-        if (c->prof_on) {
-            std::lock_guard<std::mutex> lk(c->mu);
-            if (c->prof_used == c->prof_events.size()) {
-                std::pair<cudaEvent_t, cudaEvent_t> ev;
-                cudaEventCreate(&ev.first);
-                cudaEventCreate(&ev.second);
-                c->prof_events.push_back(ev);
-            }
-            e0 = c->prof_events[c->prof_used].first;
-            e1 = c->prof_events[c->prof_used].second;
-            c->prof_used++;
-        }
+        prof_pair(c, e0, e1);
         if (e0) cudaEventRecord(e0, st);
         kern<<<grid, kThreshWarps * 32, smem, st>>>(c->tm_img, c->tm_valid, a);
         if (e1) cudaEventRecord(e1, st);
@@ -512,18 +522,7 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
     const unsigned grid = (unsigned)((tasks + kWarps - 1) / kWarps);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (c->prof_on) {
-        std::lock_guard<std::mutex> lk(c->mu);
-        if (c->prof_used == c->prof_events.size()) {
-            std::pair<cudaEvent_t, cudaEvent_t> ev;
-            cudaEventCreate(&ev.first);
-            cudaEventCreate(&ev.second);
-            c->prof_events.push_back(ev);
-        }
-        e0 = c->prof_events[c->prof_used].first;
-        e1 = c->prof_events[c->prof_used].second;
-        c->prof_used++;
-    }
+    prof_pair(c, e0, e1);
     if (e0) cudaEventRecord(e0, st);
     kern<<<grid, kWarps * 32, smem, st>>>(c->tm_img8, c->tm_info, a);
     if (e1) cudaEventRecord(e1, st);

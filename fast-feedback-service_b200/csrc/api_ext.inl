@@ -13,6 +13,9 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     a.strong_count = c->d_ext_count;
     a.chunk_count = nullptr;  // the D plane is not the connected-components input
     static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
+    cudaEvent_t e0 = nullptr, e1 = nullptr;  // ffs_profile_*: first pass + erosion + final pass together
+    prof_pair(c, e0, e1);
+    if (e0) cudaEventRecord(e0, st);
     if (brute || c->gain_brute || trusted_needs_brute(c)) {  // a gain map with non-positive entries cannot be bracketed
         a.force_brute = 1;
         resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
@@ -68,6 +71,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     f.valid_bits = c->d_ext2;
     f.valid_frame_stride = c->bits_stride;
     final_kernel<PixelT, 5><<<dim3((unsigned)(c->sm_count * 2), (unsigned)n), 256, 0, st>>>(f, c->d_valid_bits);
+    if (e1) cudaEventRecord(e1, st);
     c->launches += 3;
     FFS_CK(c, cudaGetLastError());
     return FFS_OK;

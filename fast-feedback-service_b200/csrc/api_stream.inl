@@ -9,6 +9,7 @@ static int stream_setup(ffs_ctx* c) {
     const size_t frame_bytes = (size_t)c->p.width * c->p.height * c->p.bytes_per_pixel;
     const int n_streams = std::max(1, std::min<int>((int)S, env_int("FFS_STREAMS", 4)));
     FFS_CK(c, cudaHostAlloc(&c->h_frames, frame_bytes * S, cudaHostAllocDefault));
+    if (c->pitch != (size_t)c->p.width * c->p.bytes_per_pixel) FFS_CK(c, cudaMalloc(&c->d_stage, frame_bytes * S));
     FFS_CK(c, cudaHostAlloc(&c->h_frame_counts, sizeof(uint32_t) * CNT_N * S, cudaHostAllocDefault));
     FFS_CK(c, cudaHostAlloc(&c->h_spots, sizeof(ffs_spot) * kAsyncSpots * S, cudaHostAllocDefault));
     c->streams.resize(n_streams);
@@ -30,6 +31,7 @@ static void stream_teardown(ffs_ctx* c) {
     for (auto& s : c->streams)
         if (s) cudaStreamDestroy(s);
     cudaFreeHost(c->h_frames);
+    cudaFree(c->d_stage);
     cudaFreeHost(c->h_frame_counts);
     cudaFreeHost(c->h_spots);
 }
@@ -75,10 +77,26 @@ static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st
 // connected components and the small result D2H.
 static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStream_t st) {
     if (mode == 0) {
-        const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel;
-        FFS_CK(c, cudaMemcpy2DAsync(c->d_frames + (size_t)slot * c->frame_stride, c->pitch,
-                                    c->h_frames + (size_t)slot * row * c->p.height, row, row, c->p.height,
-                                    cudaMemcpyHostToDevice, st));
+        const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel, dense = row * c->p.height;
+        uint8_t* dst = c->d_frames + (size_t)slot * c->frame_stride;
+        static const int copy2d = env_int("FFS_H2D_2D", 0);  // A/B: the pitched copy of round 1
+        if (c->pitch == row) {
+            FFS_CK(c, cudaMemcpyAsync(dst, c->h_frames + (size_t)slot * dense, dense, cudaMemcpyHostToDevice, st));
+        } else if (copy2d) {
+            FFS_CK(c, cudaMemcpy2DAsync(dst, c->pitch, c->h_frames + (size_t)slot * dense, row, row, c->p.height,
+                                        cudaMemcpyHostToDevice, st));
+        } else {
+            // one contiguous copy (the link's best case), then the row pitch on the device
+            uint8_t* stage = c->d_stage + (size_t)slot * dense;
+            FFS_CK(c, cudaMemcpyAsync(stage, c->h_frames + (size_t)slot * dense, dense, cudaMemcpyHostToDevice, st));
+            const int vb = row % 8 == 0 ? 8 : row % 4 == 0 ? 4 : 2;
+            const dim3 grid((unsigned)((row / vb + 255) / 256), c->p.height);
+            if (vb == 8) repitch_kernel<uint2><<<grid, 256, 0, st>>>(stage, row, dst, c->pitch);
+            else if (vb == 4) repitch_kernel<uint32_t><<<grid, 256, 0, st>>>(stage, row, dst, c->pitch);
+            else repitch_kernel<uint16_t><<<grid, 256, 0, st>>>(stage, row, dst, c->pitch);
+            c->launches++;
+            FFS_CK(c, cudaGetLastError());
+        }
     } else {
         int rc = bslz4_launch(c, slot, n_blocks, st);
         if (rc) return rc;

@@ -95,6 +95,7 @@ struct ffs_ctx {
     uint32_t* h_frame_counts = nullptr;  // n_slots * 8
     ffs_spot* h_spots = nullptr;         // n_slots * cap_spots
     uint8_t* h_frames = nullptr;         // n_slots dense pinned frames
+    uint8_t* d_stage = nullptr;          // n_slots dense device frames (H2D target when pitch != row bytes)
 
     // compressed ingestion (bslz4_gpu.cuh), allocated on first use
     size_t chunk_cap = 0;             // bytes per slot

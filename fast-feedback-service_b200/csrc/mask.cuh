@@ -44,6 +44,21 @@ __global__ void unpack_bits_kernel(const uint32_t* __restrict__ bits, size_t pit
     out[t] = (w >> (x & 31)) & 1u;
 }
 
+// Dense frame (rows of row_bytes) -> pitched frame (rows of pitch bytes), V = vector type of the
+// widest width that divides row_bytes.  grid (ceil(row_vecs / 256), height).  The host -> device
+// copy of a frame is ONE contiguous cudaMemcpyAsync (measured 12 % faster over PCIe than the
+// pitched cudaMemcpy2DAsync, tools/ubench/h2d.cu); this pass restores the 16-byte-aligned row
+// pitch TMA needs at HBM speed (2 x 36 MB per Eiger2 16M frame).
+template <typename V>
+__global__ void __launch_bounds__(256) repitch_kernel(const uint8_t* __restrict__ dense, size_t row_bytes,
+                                                      uint8_t* __restrict__ pitched, size_t pitch) {
+    const unsigned row_vecs = (unsigned)(row_bytes / sizeof(V));
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row_vecs) return;
+    const size_t y = blockIdx.y;
+    reinterpret_cast<V*>(pitched + y * pitch)[i] = reinterpret_cast<const V*>(dense + y * row_bytes)[i];
+}
+
 // apply_resolution_mask, kernels/masking.cu:99-147 with get_distance_from_center (:37-53)
 // and get_resolution (:64-73): float math; "0.5 * atanf()" is a double product narrowed
 // back to float exactly as the reference writes it.

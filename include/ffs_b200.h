@@ -291,8 +291,9 @@ size_t ffs_filter_spots(ffs_spot *spots, size_t n, uint32_t min_spot_size,
 /* Number of kernels this library has launched since ffs_create (all streams). */
 uint64_t ffs_kernel_launches(const ffs_ctx *ctx);
 /* Device pitch (bytes) of a frame row / bytes of one device frame / of one bit-plane. */
-/* Per-kernel timing for roofline reporting: while enabled, the dominant kernel (the
- * threshold prefilter) is bracketed by CUDA events on the stream it is launched on.
+/* Per-kernel timing for roofline reporting: while enabled, the threshold kernel of every launch
+ * (fused_dispersion_kernel; for dispersion_extended the first pass + erosion + final pass
+ * together) is bracketed by CUDA events on the stream it is launched on.
  * ffs_profile_read waits for the recorded events, returns their summed duration and the
  * number of bracketed launches, and resets both. */
 int ffs_profile_enable(ffs_ctx *ctx, int on);

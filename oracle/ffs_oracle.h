@@ -101,6 +101,12 @@ void ffs_oracle_chebyshev_to_zero(const uint8_t *plane, int width, int height, i
 int ffs_oracle_erode(const uint8_t *mask, uint8_t *plane_inout, int width, int height,
                      const ffs_oracle_params *p);
 
+/* bshuf_decompress_lz4(chunk + 12, out, n, elem_size, 0) as the frame loop calls it
+ * (spotfinder/spotfinder.cc:830-834): one HDF5 bitshuffle-LZ4 filter chunk (12-byte header +
+ * body) -> n dense elements.  0 on success (bslz4_oracle.c). */
+int ffs_oracle_bslz4_decode(const void *chunk, size_t chunk_bytes, void *out, size_t n_elements,
+                            size_t elem_size);
+
 /* Resolution mask (kernels/masking.cu:37-147), applied in place to a u8 mask. */
 void ffs_oracle_resolution_mask(uint8_t *mask, int width, int height, float wavelength,
                                 float distance_m, float beam_center_x_px,

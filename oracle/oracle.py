@@ -57,6 +57,8 @@ def build(force: bool = False) -> None:
     so = _HERE / "libffs_oracle.so"
     if so.exists():
         src_newer = max((_HERE / f).stat().st_mtime for f in ("ffs_oracle.c", "ffs_oracle.h")) > so.stat().st_mtime
+    if so.exists() and (_HERE / "bslz4_oracle.c").stat().st_mtime > so.stat().st_mtime:
+        src_newer = True
     if need or src_newer or (Path("/root/reference").exists() and not (_HERE / "_ref/libffs_ref.so").exists()):
         subprocess.run(["make", "-C", str(_HERE)], check=True, stdout=subprocess.DEVNULL)
 
@@ -82,6 +84,8 @@ def lib() -> C.CDLL:
         L.ffs_oracle_default_params.argtypes = [P]
         L.ffs_oracle_resolution_mask.restype = None
         L.ffs_oracle_resolution_mask.argtypes = [u8p, C.c_int, C.c_int] + [C.c_float] * 8
+        L.ffs_oracle_bslz4_decode.restype = C.c_int
+        L.ffs_oracle_bslz4_decode.argtypes = [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t]
         L.ffs_oracle_chebyshev_to_zero.restype = None
         L.ffs_oracle_chebyshev_to_zero.argtypes = [u8p, C.c_int, C.c_int, vp]
         L.ffs_oracle_erode.restype = C.c_int
@@ -271,6 +275,15 @@ def resolution_mask(mask, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m, 
     h, w = out.shape
     lib().ffs_oracle_resolution_mask(out.ctypes.data, w, h, wavelength, distance_m, bcx_px, bcy_px, psx_m, psy_m,
                                      dmin, dmax)
+    return out
+
+
+def bslz4_decode(chunk: bytes, dtype, n_elements: int) -> np.ndarray:
+    """bshuf_decompress_lz4(chunk + 12, out, n, elem_size, 0) (spotfinder.cc:830-834), scalar C port."""
+    out = np.empty(n_elements, dtype)
+    rc = lib().ffs_oracle_bslz4_decode(chunk, len(chunk), out.ctypes.data, n_elements, out.dtype.itemsize)
+    if rc:
+        raise ValueError(f"bslz4_decode failed: {rc}")
     return out
 
 

@@ -66,3 +66,25 @@ def test_lz4_blocks_pinned_against_liblz4():
             assert chunk[:12] == compress_chunk(a)[:12]
             rc, out = decode(chunk, n, dtype)
             assert rc == 0 and np.array_equal(out, a)
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+def test_oracle_decoder_matches_original_and_product_host_decoder(dtype):
+    """oracle/bslz4_oracle.c (the CPU arm's decoder in bench.py) on chunks from the real liblz4
+    (bslz4_encode) and from the odd-offset test encoder; corrupt input rejected."""
+    from ffs_b200 import bslz4_encode
+    from oracle import oracle
+    rng = np.random.default_rng(9)
+    for n in (8, 9, 4096, 4097, 12345, 70 * 90):
+        a = rng.poisson(3.0, n).astype(dtype)
+        a[rng.integers(0, n, max(1, n // 50))] = np.iinfo(dtype).max
+        for enc in (bslz4_encode.compress_chunk, compress_chunk):
+            chunk = enc(a)
+            assert np.array_equal(oracle.bslz4_decode(chunk, dtype, n), a)
+            rc, out = decode(chunk, n, dtype)
+            assert rc == 0 and np.array_equal(out, a)
+    chunk = bslz4_encode.compress_chunk(np.arange(5000, dtype=dtype))
+    with pytest.raises(ValueError):
+        oracle.bslz4_decode(chunk[:-9], dtype, 5000)
+    with pytest.raises(ValueError):
+        oracle.bslz4_decode(chunk, dtype, 5008)
