@@ -12,6 +12,8 @@
 #include "bslz4_gpu.cuh"
 
 #include <algorithm>
+#include <cmath>
+#include <tuple>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -96,4 +98,5 @@ static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_stro
 #include "api_stream.inl"
 #include "api_bslz4.inl"
 #include "api_sweep.inl"
+#include "api_multi.inl"
 #include "api_shim.inl"

@@ -122,6 +122,17 @@ SYMBOLS = {
     "ffs_sweep_finish": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_plane": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_sweep_export_sums": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_comm_unique_id": (_i, [_vp]),
+    "ffs_comm_create": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
+    "ffs_comm_destroy": (None, [_vp]),
+    "ffs_comm_rank": (_i, [_vp]),
+    "ffs_comm_world": (_i, [_vp]),
+    "ffs_comm_last_error": (C.c_char_p, [_vp]),
+    "ffs_sweep_merge": (_i, [_vp, _vp, C.c_uint64, C.c_uint64, _vp, _sz, C.POINTER(_vp), C.POINTER(_sz),
+                             C.POINTER(C.c_double)]),
+    "ffs_sweep_gather": (_i, [_vp, _vp, _sz, C.POINTER(_vp), C.POINTER(_sz)]),
+    "ffs_sweep_merge_host": (_i, [_i, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                  C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_set_gain": (_i, [_vp, _vp]),
     "ffs_keep_pixel_lists": (_i, [_vp, _i]),
     "ffs_last_pixel_list": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),

@@ -11,8 +11,12 @@ are unioned, and merged spots are recomputed from the exact sums with the refere
 arithmetic (double divide -> float centre of mass, float peak-centroid distance).  Canonical
 label / output order = minimum (z, linear index), as on a single GPU.
 
-`merge_slabs` is pure numpy (host logic, unit-tested on CPU); `gather_and_merge` moves the
-KB-sized tables with torch.distributed (NCCL over NVLink on GPUs, gloo in the CPU tests).
+The product's merge is native (csrc/api_multi.inl): `merge_slabs_native` = ffs_sweep_merge_host
+(slabs in one address space), `NcclComm` + `merge_native` = ffs_sweep_merge (one rank per GPU,
+boundary planes by ncclSend/ncclRecv, boundary-component records by ncclAllGather).
+`merge_slabs` below is the numpy mirror kept as the test reference of that code (unit-tested on
+CPU against the oracle's whole-sweep labelling); `gather_and_merge` moves whole slab tables with
+torch.distributed (gloo in the CPU tests) and is no longer on the bench path.
 """
 from __future__ import annotations
 
@@ -175,3 +179,129 @@ def slab_result_from(sf, z0: int, n_frames: int) -> SlabResult:
     spots = sf.sweep_finish()
     return SlabResult(z0, n_frames, spots, sf.sweep_export_sums(), sf.sweep_export_plane(0),
                       sf.sweep_export_plane(1), sf.sweep_export_moments())
+
+
+# ---- native merge (csrc/api_multi.inl) ----------------------------------------------------------
+def merge_slabs_native(slabs: list[SlabResult], width: int, height: int, with_sums: bool = False):
+    """ffs_sweep_merge_host: every slab's tables in this process -> the whole sweep's components."""
+    import ctypes as C
+    from . import lib as _lib
+    L = _lib.load()
+    n = len(slabs)
+    keep = []  # keep the arrays alive across the call
+
+    def arr(a, dtype):
+        a = np.ascontiguousarray(a, dtype=dtype)
+        keep.append(a)
+        return a.ctypes.data
+
+    z0 = arr([s.z0 for s in slabs], np.uint64)
+    nf = arr([s.n_frames for s in slabs], np.uint64)
+    have_m = all(s.moments is not None for s in slabs)
+    P = C.c_void_p * n
+    spots = P(*[arr(s.spots, SPOT_DTYPE) for s in slabs])
+    sums = P(*[arr(np.asarray(s.sums).reshape(-1), np.uint64) for s in slabs])
+    moms = P(*[arr(np.asarray(s.moments).reshape(-1), np.uint64) for s in slabs]) if have_m else None
+    first = P(*[arr(np.asarray(s.first).reshape(-1), np.uint32) for s in slabs])
+    last = P(*[arr(np.asarray(s.last).reshape(-1), np.uint32) for s in slabs])
+    S = C.c_size_t * n
+    n_spots = S(*[len(s.spots) for s in slabs])
+    n_first = S(*[len(s.first) for s in slabs])
+    n_last = S(*[len(s.last) for s in slabs])
+    out, osum, omom, n_out = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_size_t(0)
+    rc = L.ffs_sweep_merge_host(n, width, height, z0, nf, C.addressof(spots), C.addressof(n_spots), C.addressof(sums),
+                                C.addressof(moms) if moms is not None else None, C.addressof(first),
+                                C.addressof(n_first), C.addressof(last), C.addressof(n_last), C.byref(out),
+                                C.byref(osum), C.byref(omom), C.byref(n_out))
+    if rc:
+        raise _lib.FfsError(rc, "ffs_sweep_merge_host")
+
+    def take(ptr, dtype, count):
+        if not ptr.value or not count:
+            return np.zeros(count, dtype)
+        a = np.frombuffer((C.c_uint8 * (count * np.dtype(dtype).itemsize)).from_address(ptr.value), dtype=dtype).copy()
+        L.ffs_free(ptr)
+        return a
+
+    k = n_out.value
+    res = take(out, SPOT_DTYPE, k)
+    ssum = take(osum, np.uint64, 4 * k).reshape(-1, 4)
+    smom = take(omom, np.uint64, 4 * k).reshape(-1, 4)
+    return (res, ssum, smom if have_m else None) if with_sums else res
+
+
+class NcclComm:
+    """ffs_comm: one NCCL rank per GPU.  `NcclComm.from_torch()` bootstraps the unique id through
+    the process group that torchrun already set up (rank 0 creates it, a broadcast delivers it)."""
+
+    def __init__(self, unique_id: bytes, rank: int, world: int, device: int):
+        import ctypes as C
+        from . import lib as _lib
+        self._L = _lib.load()
+        h = C.c_void_p()
+        rc = self._L.ffs_comm_create(unique_id, rank, world, device, C.byref(h))
+        if rc:
+            raise _lib.FfsError(rc, "ffs_comm_create", (self._L.ffs_comm_last_error(None) or b"").decode())
+        self._h, self.rank, self.world = h, rank, world
+
+    @staticmethod
+    def unique_id() -> bytes:
+        import ctypes as C
+        from . import lib as _lib
+        buf = (C.c_uint8 * 128)()
+        rc = _lib.load().ffs_comm_unique_id(buf)
+        if rc:
+            raise _lib.FfsError(rc, "ffs_comm_unique_id")
+        return bytes(buf)
+
+    @classmethod
+    def from_torch(cls, device: int):
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        t = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{device}")
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        return cls(bytes(t.cpu().numpy().tobytes()), rank, world, device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ffs_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def merge_native(sf, comm: NcclComm, z0: int, n_frames: int, spots: np.ndarray, gather: bool = True):
+    """ffs_sweep_merge (+ ffs_sweep_gather): `spots` = sf.sweep_finish() of this rank's slab.
+    Returns (this rank's share | the whole sweep's list on every rank, exchange seconds)."""
+    import ctypes as C
+    from . import lib as _lib
+    L = sf._L
+    s = np.ascontiguousarray(spots, dtype=SPOT_DTYPE)
+    out, n_out, secs = C.c_void_p(), C.c_size_t(0), C.c_double(0)
+    rc = L.ffs_sweep_merge(sf._ctx, comm._h, z0, n_frames, s.ctypes.data, len(s), C.byref(out), C.byref(n_out),
+                           C.byref(secs))
+    if rc:
+        raise _lib.FfsError(rc, "ffs_sweep_merge", (L.ffs_last_error(sf._ctx) or b"").decode())
+
+    def take(ptr, count):
+        if not ptr.value or not count:
+            return np.zeros(0, SPOT_DTYPE)
+        a = np.frombuffer((C.c_uint8 * (count * SPOT_DTYPE.itemsize)).from_address(ptr.value), dtype=SPOT_DTYPE).copy()
+        L.ffs_free(ptr)
+        return a
+
+    mine = take(out, n_out.value)
+    if not gather:
+        return mine, secs.value
+    allp, n_all = C.c_void_p(), C.c_size_t(0)
+    rc = L.ffs_sweep_gather(comm._h, mine.ctypes.data if len(mine) else None, len(mine), C.byref(allp), C.byref(n_all))
+    if rc:
+        raise _lib.FfsError(rc, "ffs_sweep_gather", (L.ffs_comm_last_error(comm._h) or b"").decode())
+    return take(allp, n_all.value), secs.value

@@ -251,6 +251,42 @@ int ffs_sweep_export_plane(ffs_ctx *ctx, int which, uint32_t **index_and_compone
  * These are what slab merging needs; centroids alone cannot be merged. */
 int ffs_sweep_export_sums(ffs_ctx *ctx, uint64_t **sums, size_t *n_spots);
 
+/* ---- slab-sharded sweeps across GPUs: native merge, NCCL transport (csrc/api_multi.inl) ------------
+ * One rank (process or context) per GPU owns a contiguous slab of frames, streams it with sweep
+ * recording on and labels it with ffs_sweep_finish.  Components continue across a slab boundary
+ * only through identical linear indices of consecutive frames (connected_components.cc:352-370):
+ * ffs_sweep_merge sends each slab's last plane to the next rank (ncclSend / ncclRecv), all-gathers
+ * the boundary components' records and the equivalence pairs (ncclAllGather), and rebuilds the
+ * merged components from their exact integer sums.  Each rank gets ITS share of the sweep's
+ * components (those whose canonical root -- minimum (z, linear index) -- lies in its slab), z made
+ * global, canonical order; the concatenation in rank order is the order find_3d_components gives
+ * on one host (cc:292-309,396-399).  ffs_sweep_export_sums / _moments afterwards return the
+ * merged values aligned with that list.  NCCL is loaded at run time (libnccl.so.2). */
+typedef struct ffs_comm ffs_comm;
+int ffs_comm_unique_id(uint8_t *id128);  /* ncclGetUniqueId: call on one rank, hand the 128 bytes to all */
+int ffs_comm_create(const uint8_t *id128, int rank, int world, int device, ffs_comm **out);
+void ffs_comm_destroy(ffs_comm *comm);
+int ffs_comm_rank(const ffs_comm *comm);
+int ffs_comm_world(const ffs_comm *comm);
+const char *ffs_comm_last_error(const ffs_comm *comm); /* NULL: last ffs_comm_create error */
+/* spots/n_spots: what ffs_sweep_finish returned on this rank (not modified); z0 = global index of
+ * the slab's first frame, n_frames = frames in the slab.  *out_spots is freed with ffs_free.
+ * exchange_seconds (optional): time spent in the NCCL exchange. */
+int ffs_sweep_merge(ffs_ctx *ctx, ffs_comm *comm, uint64_t z0, uint64_t n_frames, const ffs_spot *spots,
+                    size_t n_spots, ffs_spot **out_spots, size_t *n_out, double *exchange_seconds);
+/* All ranks' final lists concatenated in rank order, on every rank (ncclAllGather). */
+int ffs_sweep_gather(ffs_comm *comm, const ffs_spot *mine, size_t n, ffs_spot **all, size_t *n_all);
+/* The same merge for slabs held in one address space (several contexts in one process, e.g.
+ * `spotfinder --devices`): plain host arrays per slab -- spots, sums (4 per spot), moments (4 per
+ * spot, may be NULL), first / last plane as {index, component} pairs -- no transport, no GPU.
+ * Outputs (ffs_free): the whole sweep's components in canonical order with merged sums/moments. */
+int ffs_sweep_merge_host(int n_slabs, uint32_t width, uint32_t height, const uint64_t *z0,
+                         const uint64_t *n_frames, const ffs_spot *const *spots, const size_t *n_spots,
+                         const uint64_t *const *sums, const uint64_t *const *moments,
+                         const uint32_t *const *first, const size_t *n_first,
+                         const uint32_t *const *last, const size_t *n_last, ffs_spot **out_spots,
+                         uint64_t **out_sums, uint64_t **out_moments, size_t *n_out);
+
 /* ---- per-spot variances in Kabsch space (Reflection3D::variances_in_kabsch_space,
  *      connected_components.cc:159-203; caller loop spotfinder.cc:1152-1216) ----------------
  * Second moments of each 3D component of the last ffs_sweep_finish, same order, 4 per spot,

@@ -23,7 +23,7 @@ def _frames(dtype, n=2):
     mask = synth.make_mask(g)
     # no hot pixels: the reference evaluates pixel*pixel in the narrow type (N13, thresholding.cu:95-97)
     frames = synth.make_frames(g, mask, n, dtype, config=6, n_spots=60, n_hot=0)
-    frames[mask == 0] = 0  # gap value irrelevant (masked) but keeps N13 out of the picture entirely
+    frames[:, mask == 0] = 0  # gap value irrelevant (masked) but keeps N13 out of the picture entirely
     return g, mask, frames
 
 

@@ -9,7 +9,7 @@ import pytest
 
 from ffs_b200 import synth
 from ffs_b200.lib import SPOT_DTYPE
-from ffs_b200.sweep import SlabResult, merge_slabs, slab_bounds
+from ffs_b200.sweep import SlabResult, merge_slabs, merge_slabs_native, slab_bounds
 from oracle import oracle
 
 INT_FIELDS = ["label", "x_min", "x_max", "y_min", "y_max", "z_min", "z_max", "num_pixels", "peak_x", "peak_y",
@@ -67,6 +67,11 @@ def test_merge_matches_whole_sweep(world):
     if world > 1:  # slab cuts really split components
         assert sum(len(s.spots) for s in slabs) > len(want)
     check(merge_slabs(slabs, g.width, g.height), want)
+    # the product's native merge (csrc/api_multi.inl, ffs_sweep_merge_host: plain host code, no GPU)
+    native = merge_slabs_native(slabs, g.width, g.height)
+    check(native, want)
+    for f in ("com_x", "com_y", "com_z", "peak_centroid_distance"):  # same float operations as the device
+        assert np.array_equal(native[f], merge_slabs(slabs, g.width, g.height)[f], equal_nan=True), f
 
 
 @pytest.mark.parametrize("world", [2, 4])
@@ -79,6 +84,10 @@ def test_merged_sums_and_moments_are_exact(world):
     check(spots, whole.spots)
     assert np.array_equal(sums, whole.sums)
     assert np.array_equal(moments, whole.moments)
+    nspots, nsums, nmom = merge_slabs_native(slabs, g.width, g.height, with_sums=True)
+    check(nspots, whole.spots)
+    assert np.array_equal(nsums, whole.sums)
+    assert np.array_equal(nmom, whole.moments)
 
 
 def test_oracle_kabsch_variances_known_answers():
@@ -112,6 +121,11 @@ def test_component_spanning_three_slabs_and_empty_boundary():
     _, want = oracle.connected_components(strong, sweep, want_labels=False)
     slabs = [oracle_slab(strong, sweep, z, z + 1) for z in range(6)]  # one frame per "rank"
     check(merge_slabs(slabs, g.width, g.height), want)
+    check(merge_slabs_native(slabs, g.width, g.height), want)
+    check(merge_slabs_native(slabs[::-1], g.width, g.height), want)  # slab order is by z0, not by position
+    # non-adjacent slabs (a missing frame between them) must not be joined
+    gap = [oracle_slab(strong, sweep, 0, 2), oracle_slab(strong, sweep, 4, 6)]
+    assert len(merge_slabs_native(gap, g.width, g.height)) == len(gap[0].spots) + len(gap[1].spots)
 
 
 def _worker(rank, world, port, q):
