@@ -548,22 +548,28 @@ def sweep_leg(cfg, env, n_frames_total):
     sys.path.insert(0, str(ROOT / "tools"))
     from bench_sweep import SweepSource, run_slab
     from ffs_b200.spotfinder import Spotfinder
-    from ffs_b200.sweep import gather_and_merge, slab_bounds
+    from ffs_b200.sweep import NcclComm, merge_native, merge_slabs_native, slab_bounds
     g = cfg["geom"]
     mask = synth.make_mask(g)
     src = SweepSource(g, mask, n_frames_total, cfg["dtype"])
     z0, z1 = slab_bounds(n_frames_total, env["world"], env["rank"])
     times = {}
+    comm = NcclComm.from_torch(env["local"]) if env["world"] > 1 else None
     with Spotfinder(g.width, g.height, cfg["dtype"], mask, n_slots=6, device=env["local"]) as sf:
         slab = run_slab(sf, src, z0, z1, times)
         env["barrier"]()
         tm = time.perf_counter()
-        merged = gather_and_merge(slab, g.width, g.height)
+        if comm is not None:  # native merge over NCCL (csrc/api_multi.inl)
+            merged, times["exchange_s"] = merge_native(sf, comm, z0, z1 - z0, slab.spots, gather=True)
+        else:
+            merged, times["exchange_s"] = merge_slabs_native([slab], g.width, g.height), 0.0
         torch.cuda.synchronize()
         times["merge_s"] = time.perf_counter() - tm
         kept, _, _ = sf.filter_spots(merged, 3, 2.0)
     times.update(frames=n_frames_total, components=int(len(merged)), spots_after_filters=int(len(kept)),
                  slab_components=int(len(slab.spots)))
+    if comm is not None:
+        comm.close()
     return times
 
 
@@ -615,6 +621,8 @@ def run_gpu_arm(args):
                            "h2d_bytes_per_step": t["frames"] * frame_bytes // world, "d2h_bytes_per_step": 0},
                    "sweep": {"stream_s": stream_s, "synth_s_inside_stream": synth_s, "finish_3d_s": finish_s,
                              "merge_s": merge_s, "components": t["components"],
+                             "merge": "native (csrc/api_multi.inl): ncclSend/ncclRecv of boundary planes + "
+                                      "ncclAllGather of boundary-component records" if world > 1 else "single slab",
                              "spots_after_filters": t["spots_after_filters"],
                              "labelling_frames_per_s": t["frames"] / (finish_s + merge_s)},
                    "gpu_launches": None}

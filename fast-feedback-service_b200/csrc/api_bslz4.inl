@@ -158,6 +158,10 @@ extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, si
     }
     FFS_CK(c, cudaSetDevice(c->p.device));
     cudaStream_t st = c->streams[s.stream];
+    if (c->frame_timing) {  // "Copy" of the timing report starts with the chunk's upload
+        if (!s.t_ev[0]) FFS_CK(c, cudaEventCreate(&s.t_ev[0]));
+        FFS_CK(c, cudaEventRecord(s.t_ev[0], st));
+    }
     // the two uploads whose sizes change from frame to frame stay outside the slot's graph
     FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, chunk, chunk_bytes,
                               cudaMemcpyHostToDevice, st));

@@ -25,6 +25,8 @@ static int stream_setup(ffs_ctx* c) {
 static void stream_teardown(ffs_ctx* c) {
     for (auto& s : c->slots) {
         if (s.done) cudaEventDestroy(s.done);
+        for (auto& e : s.t_ev)
+            if (e) cudaEventDestroy(e);
         for (auto& g : s.graph)
             if (g) cudaGraphExecDestroy(g);
     }
@@ -76,6 +78,12 @@ static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st
 // pinned frame; mode 1: decode of the (already uploaded) compressed chunk.  Then threshold,
 // connected components and the small result D2H.
 static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStream_t st) {
+    cudaEvent_t* tev = c->frame_timing ? c->slots[slot].t_ev : nullptr;
+    if (tev) {
+        for (int k = 0; k < 4; ++k)
+            if (!tev[k]) FFS_CK(c, cudaEventCreate(&tev[k]));
+        if (mode == 0) FFS_CK(c, cudaEventRecord(tev[0], st));  // (compressed: recorded before the chunk's H2D)
+    }
     if (mode == 0) {
         const size_t row = (size_t)c->p.width * c->p.bytes_per_pixel, dense = row * c->p.height;
         uint8_t* dst = c->d_frames + (size_t)slot * c->frame_stride;
@@ -103,13 +111,16 @@ static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStre
         FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + slot, sizeof(unsigned),
                                   cudaMemcpyDeviceToHost, st));
     }
+    if (tev) FFS_CK(c, cudaEventRecord(tev[1], st));
     int rc = threshold_impl(c, slot, 1, st);
     if (rc == FFS_OK) rc = cc_impl(c, slot, 1, st);
     if (rc) return rc;
+    if (tev) FFS_CK(c, cudaEventRecord(tev[2], st));
     FFS_CK(c, cudaMemcpyAsync(c->h_frame_counts + (size_t)slot * CNT_N, c->d_frame_counts + (size_t)slot * CNT_N,
                               sizeof(uint32_t) * CNT_N, cudaMemcpyDeviceToHost, st));
     FFS_CK(c, cudaMemcpyAsync(c->h_spots + (size_t)slot * kAsyncSpots, c->d_spots + (size_t)slot * c->cap_spots,
                               sizeof(ffs_spot) * std::min(kAsyncSpots, c->cap_spots), cudaMemcpyDeviceToHost, st));
+    if (tev) FFS_CK(c, cudaEventRecord(tev[3], st));
     return FFS_OK;
 }
 
@@ -120,7 +131,7 @@ static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStre
 static int submit_tail(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, uint64_t frame_id, cudaStream_t st) {
     StreamSlot& s = c->slots[slot];
     static const int use_graph = env_int("FFS_GRAPH", 1);
-    const bool graph_ok = use_graph && !c->prof_on && s.uses[mode] >= 1;
+    const bool graph_ok = use_graph && !c->prof_on && !c->frame_timing && s.uses[mode] >= 1;
     if (graph_ok && s.graph[mode] && mode == 1 && s.graph_blocks != n_blocks) {
         cudaGraphExecDestroy(s.graph[mode]);  // block size changed: rebuild
         s.graph[mode] = nullptr;
@@ -202,6 +213,11 @@ extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, s
     FFS_CK(c, cudaEventSynchronize(s.done));
     const uint32_t* cnt = c->h_frame_counts + (size_t)slot * CNT_N;
     if (result) counts_to_result(cnt, s.frame_id, result);
+    if (c->frame_timing && s.t_ev[3]) {
+        for (int k = 0; k < 3; ++k)
+            if (cudaEventElapsedTime(&c->last_timing[k], s.t_ev[k], s.t_ev[k + 1]) != cudaSuccess) c->last_timing[k] = 0;
+        cudaGetLastError();
+    }
     if (s.compressed && c->h_dec_status && c->h_dec_status[slot] != 0) {
         // malformed bitshuffle-LZ4 input: the frame was not decoded, its result is void
         if (result) result->status = FFS_ERR_FORMAT;
@@ -250,6 +266,22 @@ extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, s
     }
     c->cv.notify_all();
     return rc;
+}
+
+// Per-image timing of the reference's `--threads 1` report (spotfinder.cc:1055-1076).
+extern "C" int ffs_frame_timing(ffs_ctx* c, int on) {
+    if (!c) return FFS_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->frame_timing = on != 0;
+    return FFS_OK;
+}
+
+extern "C" int ffs_last_frame_timing(ffs_ctx* c, float* copy_ms, float* kernel_ms, float* post_copy_ms) {
+    if (!c || !c->frame_timing) return FFS_ERR_ARG;
+    if (copy_ms) *copy_ms = c->last_timing[0];
+    if (kernel_ms) *kernel_ms = c->last_timing[1];
+    if (post_copy_ms) *post_copy_ms = c->last_timing[2];
+    return FFS_OK;
 }
 
 extern "C" int ffs_keep_pixel_lists(ffs_ctx* c, int on) {

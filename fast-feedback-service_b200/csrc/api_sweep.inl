@@ -16,11 +16,16 @@ extern "C" int ffs_sweep_begin(ffs_ctx* c, uint64_t max_frames) {
     c->sweep_plane[1].clear();
     c->sweep_sums.clear();
     c->sweep_moments.clear();
+    c->sweep_overflow = false;
     return FFS_OK;
 }
 
 // called from ffs_wait / ffs_sweep_record_slot once the slot's results are complete
 static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_strong) {
+    // a frame whose strong-pixel list hit its capacity would contribute a truncated plane and the
+    // 3D components would come out wrong without notice: remember it, ffs_sweep_finish refuses
+    if ((int32_t)c->h_frame_counts[(size_t)slot * CNT_N + CNT_STATUS] != 0 && c->slots[slot].state == 2)
+        c->sweep_overflow = true;
     std::vector<uint32_t> idx(n_strong), val(n_strong);
     if (n_strong) {
         FFS_CK(c, cudaMemcpy(idx.data(), c->d_px_index + (size_t)slot * c->cap_strong, n_strong * 4ull,
@@ -57,10 +62,22 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     std::vector<size_t> order(nz);
     for (size_t i = 0; i < nz; ++i) order[i] = i;
     std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return c->sweep_ids[x] < c->sweep_ids[y]; });
-    std::vector<uint32_t> fo(nz + 1, 0);
-    for (size_t z = 0; z < nz; ++z) fo[z + 1] = fo[z] + (uint32_t)c->sweep_index[order[z]].size();
-    const size_t total = fo[nz];
     c->sweep_on = false;
+    if (c->sweep_overflow) {
+        c->err = "a frame of the sweep exceeded max_strong_per_frame: 3D components would be wrong";
+        return FFS_ERR_CAPACITY;
+    }
+    std::vector<uint32_t> fo(nz + 1, 0);
+    uint64_t total64 = 0;
+    for (size_t z = 0; z < nz; ++z) {
+        total64 += c->sweep_index[order[z]].size();
+        fo[z + 1] = (uint32_t)total64;
+    }
+    if (total64 >= 0xffffffffull) {  // compact ids are 32-bit
+        c->err = "sweep holds more than 2^32 strong pixels";
+        return FFS_ERR_CAPACITY;
+    }
+    const size_t total = (size_t)total64;
     if (total == 0) return FFS_OK;
     std::vector<uint32_t> idx(total), val(total), zarr(total);
     for (size_t z = 0; z < nz; ++z) {
@@ -76,7 +93,10 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     ffs_spot* d_spots = nullptr;
     unsigned long long *d_sums = nullptr, *d_mom = nullptr;
     int rc = FFS_OK;
+    ffs_spot* out = nullptr;
+    bool keep_out = false;
     auto cleanup = [&]() {
+        if (!keep_out) free(out);
         cudaFree(d_fo); cudaFree(d_idx); cudaFree(d_val); cudaFree(d_z); cudaFree(d_par);
         cudaFree(d_rank); cudaFree(d_n); cudaFree(d_acc); cudaFree(d_spots); cudaFree(d_sums); cudaFree(d_mom);
     };
@@ -126,7 +146,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
     uint32_t n = 0;
     SWEEP_CK(cudaMemcpyAsync(&n, d_n, 4, cudaMemcpyDeviceToHost, c->stream));
     SWEEP_CK(cudaStreamSynchronize(c->stream));
-    ffs_spot* out = n ? (ffs_spot*)malloc(sizeof(ffs_spot) * n) : nullptr;
+    out = n ? (ffs_spot*)malloc(sizeof(ffs_spot) * n) : nullptr;
     if (n && !out) {
         cleanup();
         return FFS_ERR_NOMEM;
@@ -153,6 +173,7 @@ extern "C" int ffs_sweep_finish(ffs_ctx* c, ffs_spot** spots_out, size_t* n_out)
         }
     }
 #undef SWEEP_CK
+    keep_out = true;
     cleanup();
     *spots_out = out;
     *n_out = n;

@@ -31,6 +31,7 @@ struct SpotfinderArgs {
     bool save_h5 = false;
     bool output_for_index = false;
     bool list_devices = false;
+    std::vector<int> devices;    // --devices 0,1,2 | 0-7: frame-wise sharding over several GPUs (extension)
 };
 
 inline void print_usage(const char* prog) {
@@ -39,7 +40,7 @@ inline void print_usage(const char* prog) {
       "       [--images N] [--writeout] [--min-spot-size N] [--min-spot-size-3d N]\n"
       "       [--max-peak-centroid-separation F] [--start-index N] [-t SECONDS] [-fd FD]\n"
       "       [-a dispersion|dispersion_extended] [--dmin F] [--dmax F] [-w ANGSTROM]\n"
-      "       [--detector JSON] [-h5] [--output-for-index] [--sample | FILE.nxs]\n\n"
+      "       [--detector JSON] [-h5] [--output-for-index] [--devices LIST] [--sample | FILE.nxs]\n\n"
       "Positional: FILE.nxs  Path to the Nexus file, or a /dev/shm Eiger stream directory\n",
       prog);
 }
@@ -89,6 +90,20 @@ inline bool parse_args(int argc, char** argv, const char* version, SpotfinderArg
             else if (s == "--dmax") { if (!(v = need(i, s))) return false; a.dmax = std::stof(*v); }
             else if (s == "-w" || s == "-\xCE\xBB" || s == "--wavelength") { if (!(v = need(i, s))) return false; a.wavelength = std::stof(*v); }
             else if (s == "--detector") { if (!(v = need(i, s))) return false; a.detector = *v; }
+            else if (s == "--devices") {  // "0,1,2" and/or "0-7"
+                if (!(v = need(i, s))) return false;
+                size_t pos = 0;
+                while (pos < v->size()) {
+                    size_t end = v->find(',', pos);
+                    if (end == std::string::npos) end = v->size();
+                    const std::string tok = v->substr(pos, end - pos);
+                    const size_t dash = tok.find('-');
+                    const int lo = std::stoi(tok.substr(0, dash));
+                    const int hi = dash == std::string::npos ? lo : std::stoi(tok.substr(dash + 1));
+                    for (int d = lo; d <= hi; ++d) a.devices.push_back(d);
+                    pos = end + 1;
+                }
+            }
             else if (!s.empty() && s[0] == '-' && s.size() > 1 && !std::isdigit((unsigned char)s[1])) {
                 printf("Error: Unknown argument: %s\n", s.c_str());
                 return false;

@@ -13,11 +13,30 @@
     p.trusted_max = (int64_t)(pixel_t)reader.get_trusted_range()[1];
     p.device = args.device;
     p.n_slots = (int32_t)std::min<uint32_t>(std::max<uint32_t>(args.threads + 2, 6), 24);
-    ffs_ctx* ctx = nullptr;
-    if (int rc = ffs_create(&p, reader.get_mask().data(), &ctx)) {
-        printf("Error: could not initialise the GPU spotfinder (%d): %s\n", rc, ffs_last_error(nullptr));
-        return 1;
+    // One context (buffers, streams, pinned ring) per GPU.  `--devices` shards the stream frame by
+    // frame over several GPUs inside this process, as the reference shards it over host threads
+    // (shared atomic frame counter, spotfinder.cc:686,752); -d/--device alone is the reference's CLI.
+    std::vector<int> devices = args.devices.empty() ? std::vector<int>{args.device} : args.devices;
+    const size_t n_dev = devices.size();
+    if (n_dev > 1) {
+        printf("Sharding frames over %zu GPUs:", n_dev);
+        for (int d : devices) printf(" %d", d);
+        printf("\n");
     }
+    std::vector<ffs_ctx*> ctxs(n_dev, nullptr);
+    auto destroy_all = [&]() {
+        for (ffs_ctx* c : ctxs) ffs_destroy(c);
+    };
+    for (size_t d = 0; d < n_dev; ++d) {
+        p.device = devices[d];
+        if (int rc = ffs_create(&p, reader.get_mask().data(), &ctxs[d])) {
+            printf("Error: could not initialise the GPU spotfinder on device %d (%d): %s\n", devices[d], rc,
+                   ffs_last_error(nullptr));
+            destroy_all();
+            return 1;
+        }
+    }
+    ffs_ctx* ctx = ctxs[0];
     printf("Mask has %llu valid pixels of %u\n", (unsigned long long)ffs_mask_valid_count(ctx), width * height);
     // --writeout (spotfinder.cc:626-646,653-679): white = valid, red = masked
     auto write_mask_png = [&](const char* name, const uint8_t* m) {
@@ -28,28 +47,47 @@
     };
     if (args.writeout) {
         write_mask_png("mask_source.png", reader.get_mask().data());
-        ffs_keep_pixel_lists(ctx, 2);
+        for (ffs_ctx* c : ctxs) ffs_keep_pixel_lists(c, 2);
     }
     if (args.dmin > 0 || args.dmax > 0) {  // apply_resolution_filtering, spotfinder.cc:110-137,650-652
-        if (ffs_apply_resolution_mask(ctx, wavelength, det.distance, det.beam_center_x, det.beam_center_y,
-                                      det.pixel_size_x, det.pixel_size_y, args.dmin, args.dmax)) {
-            printf("Error: resolution mask failed: %s\n", ffs_last_error(ctx));
-            return 1;
-        }
+        for (ffs_ctx* c : ctxs)
+            if (ffs_apply_resolution_mask(c, wavelength, det.distance, det.beam_center_x, det.beam_center_y,
+                                          det.pixel_size_x, det.pixel_size_y, args.dmin, args.dmax)) {
+                printf("Error: resolution mask failed: %s\n", ffs_last_error(c));
+                destroy_all();
+                return 1;
+            }
         printf("Resolution mask applied: %llu valid pixels remain\n", (unsigned long long)ffs_mask_valid_count(ctx));
         if (args.writeout) {
             std::vector<uint8_t> calc((size_t)width * height);
             if (ffs_get_mask(ctx, calc.data()) == FFS_OK) write_mask_png("mask_calculated.png", calc.data());
         }
     }
+    // --threads 1: the per-image Copy / Kernel / Post Copy report (spotfinder.cc:1055-1076)
+    const bool timing_report = args.threads == 1;
+    if (timing_report)
+        for (ffs_ctx* c : ctxs) ffs_frame_timing(c, 1);
     if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain; use tests/validate_stream.py\n");
     if (args.save_h5) printf("Note: results_ffs.h5 cannot be written by this build (libhdf5 unavailable)\n");
     std::unique_ptr<PipeHandler> pipe;
     if (args.pipe_fd != -1) pipe = std::make_unique<PipeHandler>(args.pipe_fd);
-    if (rotation) ffs_sweep_begin(ctx, num_images);
+    // Rotation data: every GPU owns a CONTIGUOUS slab of frames (3D components couple consecutive
+    // frames only), labels it, and the slabs are merged at the end (ffs_sweep_merge_host).
+    auto device_of = [&](uint32_t image_num) -> size_t {
+        if (n_dev == 1) return 0;
+        return rotation ? std::min<size_t>(n_dev - 1, (size_t)image_num * n_dev / num_images) : image_num % n_dev;
+    };
+    auto slab_begin = [&](size_t d) -> uint32_t {  // first frame with device_of(frame) == d
+        return (uint32_t)(((uint64_t)d * num_images + n_dev - 1) / n_dev);
+    };
+    if (rotation)
+        for (size_t d = 0; d < n_dev; ++d) ffs_sweep_begin(ctxs[d], num_images / n_dev + 1);
 
     const size_t px = (size_t)width * height;
-    std::atomic<uint32_t> next_image{0}, submitted{0}, completed{0};
+    std::atomic<uint32_t> next_image{0}, completed{0};
+    std::vector<std::atomic<uint32_t>> submitted(n_dev), collected(n_dev);
+    for (size_t d = 0; d < n_dev; ++d) submitted[d] = collected[d] = 0;
+    std::mutex print_mutex;
     std::atomic<int> workers_alive{(int)args.threads};
     std::atomic<bool> had_error{false};
     std::atomic<uint32_t> failed_images{0};
@@ -67,6 +105,8 @@
             const uint32_t image_num = next_image.fetch_add(1);
             if (image_num >= num_images) break;
             const size_t offset_image_num = image_num + args.start_index;
+            const size_t dev = device_of(image_num);
+            ffs_ctx* ctx = ctxs[dev];
             {   // availability poll every 100 ms, abort after `timeout` s without a new image (:770-787)
                 const auto wait_start = clk::now();
                 while (!reader.is_image_available(offset_image_num) && !g_stop) {
@@ -135,19 +175,20 @@
                 had_error = true;
                 break;
             }
-            submitted++;
+            submitted[dev]++;
         }
         workers_alive--;
     };
 
-    auto collector = [&]() {
+    auto collector = [&](size_t dev) {
+        ffs_ctx* ctx = ctxs[dev];
         std::vector<ffs_spot> spots(65536);
         for (;;) {
             ffs_frame_result r;
             size_t n = 0;
             const int rc = ffs_wait(ctx, &r, spots.data(), spots.size(), &n);
             if (rc == FFS_ERR_STATE) {
-                if (workers_alive == 0 && completed >= submitted) break;
+                if (workers_alive == 0 && collected[dev] >= submitted[dev]) break;
                 std::this_thread::sleep_for(200us);
                 continue;
             }
@@ -156,7 +197,7 @@
                 printf("Error: %s\n", ffs_last_error(ctx));
                 g_stop = true;
                 had_error = true;
-                completed++;
+                collected[dev]++;
                 continue;
             }
             if (r.status == FFS_ERR_FORMAT) {
@@ -165,9 +206,10 @@
                 printf("Error: could not decompress image %llu\n", (unsigned long long)r.frame_id);
                 had_error = true;
                 failed_images++;
-                completed++;
+                collected[dev]++;
                 continue;
             }
+            std::lock_guard<std::mutex> plk(print_mutex);  // one image's lines stay together
             if (r.status != 0)
                 printf("Warning: image %llu exceeded a spot-list capacity; results truncated\n", (unsigned long long)r.frame_id);
             if (n > spots.size()) n = spots.size();
@@ -239,27 +281,81 @@
                     if (!pngw::write_rgb(name, rgb.data(), width, height)) printf("Warning: could not write %s\n", name);
                 }
             }
-            printf("Thread %2d finished image %4u with %5u strong pixels, %4u filtered reflections (%u pixels)\n",
-                   thread_of[image_num], image_num, r.num_strong_pixels, r.n_spots_total, r.num_strong_pixels_filtered);
+            float t_copy = 0, t_kernel = 0, t_post = 0;
+            if (timing_report && ffs_last_frame_timing(ctx, &t_copy, &t_kernel, &t_post) == FFS_OK) {
+                // the reference's single-thread block (spotfinder.cc:1055-1076); "Post" is its host-side
+                // connected components, which run inside "Kernel" here
+                const float total = t_copy + t_kernel + t_post;
+                printf("Thread %2d finished image %4u\n"
+                       "       Copy: %5.1f ms\n"
+                       "     Kernel: %5.1f ms\n"
+                       "  Post Copy: %5.1f ms\n"
+                       "       Post: %5.1f ms\n"
+                       "             \xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\xE2\x95\x90\n"
+                       "     Total:  %5.1f ms (%.1f GBps)\n"
+                       "    \033[1m%u\033[0m strong pixels\n"
+                       "    \033[1m%u\033[0m filtered reflections (\033[1m%u\033[0m pixels)\n",
+                       thread_of[image_num], image_num, t_copy, t_kernel, t_post, 0.0f, total,
+                       total > 0 ? (float)((double)px * sizeof(pixel_t) / (total * 1e-3) / 1e9) : 0.0f,
+                       r.num_strong_pixels, r.n_spots_total, r.num_strong_pixels_filtered);
+            } else {
+                printf("Thread %2d finished image %4u with %5u strong pixels, %4u filtered reflections (%u pixels)\n",
+                       thread_of[image_num], image_num, r.num_strong_pixels, r.n_spots_total,
+                       r.num_strong_pixels_filtered);
+            }
             completed++;
+            collected[dev]++;
         }
     };
 
     {
         std::vector<std::thread> threads;
         for (uint32_t t = 0; t < args.threads; ++t) threads.emplace_back(worker, (int)t);
-        std::thread coll(collector);
+        std::vector<std::thread> colls;
+        for (size_t d = 0; d < n_dev; ++d) colls.emplace_back(collector, d);
         for (auto& t : threads) t.join();
-        coll.join();
+        for (auto& t : colls) t.join();
     }
 
     if (rotation) {  // spotfinder.cc:1099-1150 + find_3d_components (connected_components.cc:448-470)
         printf("Processing 3D spots\n");
         ffs_spot* s3 = nullptr;
         size_t n3 = 0;
-        if (ffs_sweep_finish(ctx, &s3, &n3) != FFS_OK) {
-            printf("Error: 3D connected components failed: %s\n", ffs_last_error(ctx));
-            return 1;
+        uint64_t *msums = nullptr, *mmoments = nullptr;  // merged sums / moments (several GPUs)
+        if (n_dev == 1) {
+            if (ffs_sweep_finish(ctx, &s3, &n3) != FFS_OK) {
+                printf("Error: 3D connected components failed: %s\n", ffs_last_error(ctx));
+                return 1;
+            }
+        } else {
+            // every GPU labels its slab; slabs are merged through their boundary planes (csrc/api_multi.inl)
+            std::vector<ffs_spot*> sp(n_dev, nullptr);
+            std::vector<size_t> ns(n_dev, 0), nfirst(n_dev, 0), nlast(n_dev, 0);
+            std::vector<uint64_t*> sums(n_dev, nullptr), moms(n_dev, nullptr);
+            std::vector<uint32_t*> first(n_dev, nullptr), last(n_dev, nullptr);
+            std::vector<uint64_t> z0(n_dev), nf(n_dev);
+            bool ok = true;
+            for (size_t d = 0; d < n_dev && ok; ++d) {
+                size_t n_s = 0, n_m = 0;
+                ok = ffs_sweep_finish(ctxs[d], &sp[d], &ns[d]) == FFS_OK &&
+                     ffs_sweep_export_sums(ctxs[d], &sums[d], &n_s) == FFS_OK &&
+                     ffs_sweep_export_moments(ctxs[d], &moms[d], &n_m) == FFS_OK &&
+                     ffs_sweep_export_plane(ctxs[d], 0, &first[d], &nfirst[d]) == FFS_OK &&
+                     ffs_sweep_export_plane(ctxs[d], 1, &last[d], &nlast[d]) == FFS_OK;
+                if (!ok) printf("Error: 3D connected components failed on device %d: %s\n", devices[d], ffs_last_error(ctxs[d]));
+                z0[d] = slab_begin(d);
+                nf[d] = (d + 1 < n_dev ? slab_begin(d + 1) : num_images) - slab_begin(d);
+            }
+            if (ok && ffs_sweep_merge_host((int)n_dev, width, height, z0.data(), nf.data(), sp.data(), ns.data(),
+                                           sums.data(), moms.data(), first.data(), nfirst.data(), last.data(),
+                                           nlast.data(), &s3, &msums, &mmoments, &n3) != FFS_OK) {
+                printf("Error: slab merge failed\n");
+                ok = false;
+            }
+            for (size_t d = 0; d < n_dev; ++d) {
+                ffs_free(sp[d]); ffs_free(sums[d]); ffs_free(moms[d]); ffs_free(first[d]); ffs_free(last[d]);
+            }
+            if (!ok) return 1;
         }
         printf("Calculated %zu spots\n", n3);
         // Kabsch-space variances of every component (spotfinder.cc:1152-1196), evaluated before
@@ -279,7 +375,13 @@
             kg.pixel_size_y_mm = det.pixel_size_y * 1000;
             kg.wavelength = wavelength;
             kg.oscillation_width_deg = oscillation_width;
-            if (ffs_sweep_export_sums(ctx, &sums, &ns) != FFS_OK || ffs_sweep_export_moments(ctx, &moments, &nm) != FFS_OK ||
+            if (n_dev > 1) {
+                sums = msums;
+                moments = mmoments;
+                ns = nm = n3;
+            }
+            if ((n_dev == 1 && (ffs_sweep_export_sums(ctx, &sums, &ns) != FFS_OK ||
+                                ffs_sweep_export_moments(ctx, &moments, &nm) != FFS_OK)) ||
                 ns != n3 || nm != n3 ||
                 ffs_kabsch_variances(ctx, &kg, s3, sums, moments, n3, var_b.data(), var_m.data(), depth.data()) != FFS_OK) {
                 printf("Error: spot variance calculation failed: %s\n", ffs_last_error(ctx));
@@ -328,6 +430,6 @@
     else
         printf("Total time waiting for images to appear: %.2f s\n", time_waiting_for_images);
     pipe.reset();
-    ffs_destroy(ctx);
+    destroy_all();
     // a run that stopped on an error must not look like a clean one to the calling service
     return had_error ? 1 : 0;

@@ -35,6 +35,7 @@ struct StreamSlot {
     uint32_t graph_kernels[2] = {0, 0};  // kernels inside each graph (launch accounting)
     uint32_t graph_blocks = 0;           // bitshuffle blocks the compressed graph was built for
     uint32_t uses[2] = {0, 0};
+    cudaEvent_t t_ev[4] = {nullptr, nullptr, nullptr, nullptr};  // ffs_frame_timing: start, copied, kernels, done
 };
 
 }  // namespace ffsb
@@ -133,10 +134,13 @@ struct ffs_ctx {
 
     // sweep (3D) recording
     bool sweep_on = false;
+    bool sweep_overflow = false;  // a recorded frame hit a capacity: ffs_sweep_finish refuses
     std::vector<uint64_t> sweep_ids;
     std::vector<std::vector<uint32_t>> sweep_index;  // per frame strong-pixel linear indices
     std::vector<std::vector<uint32_t>> sweep_value;
     std::vector<uint64_t> sweep_sums;      // per 3D component: exact sum I, (2x+1)I, (2y+1)I, (2z+1)I
+    bool frame_timing = false;             // ffs_frame_timing: per-frame copy / kernel / post-copy times
+    float last_timing[3] = {0, 0, 0};      // of the last ffs_wait frame, ms
     bool keep_pixels = false;              // ffs_keep_pixel_lists
     bool keep_frame = false;
     std::vector<uint8_t> last_frame;       // dense pixels of the last ffs_wait frame (keep mode 2)

@@ -224,6 +224,12 @@ int ffs_decode_chunk_device(ffs_ctx *ctx, int slot, const void *chunk, size_t ch
  * ffs_wait on this context.  on = 2 also keeps the dense frame as the device saw it (after the
  * device decode, if any), for the diagnostic picture. */
 int ffs_keep_pixel_lists(ffs_ctx *ctx, int on);
+/* The per-image timing block the reference prints with --threads 1 (spotfinder.cc:1055-1076: Copy /
+ * Kernel / Post Copy): while on, every streamed frame is bracketed by CUDA events (and replayed
+ * without its graph); ffs_last_frame_timing returns the times of the last ffs_wait frame in ms:
+ * host->device copy (or upload + device decode), threshold + connected components, result copy. */
+int ffs_frame_timing(ffs_ctx *ctx, int on);
+int ffs_last_frame_timing(ffs_ctx *ctx, float *copy_ms, float *kernel_ms, float *post_copy_ms);
 int ffs_last_pixel_list(ffs_ctx *ctx, const uint32_t **index, size_t *n);
 int ffs_last_frame(ffs_ctx *ctx, const void **pixels, size_t *bytes);
 

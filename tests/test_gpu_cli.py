@@ -222,3 +222,63 @@ def test_list_devices_and_bad_args():
     assert out.returncode == 0 and re.search(r"0: .+ \(CUDA \d+\.\d+\)", out.stdout)  # service.py:220-238 probes this
     assert subprocess.run([str(BIN / "spotfinder")], capture_output=True).returncode == 1
     assert subprocess.run([str(BIN / "spotfinder"), "/tmp", "-a", "sobel"], capture_output=True).returncode == 1
+
+
+def test_single_thread_timing_block(tmp_path):
+    """--threads 1 (the default) prints the reference's per-image Copy / Kernel / Post Copy block
+    (spotfinder.cc:1055-1076) instead of the one-line multi-thread report."""
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 3, np.uint16, config=8, n_spots=12)
+    write_stream(tmp_path, frames, mask, 16)
+    rc, lines, out, err = run("spotfinder", [str(tmp_path)])
+    assert rc == 0 and err == "" and len(lines) == 3
+    plain = re.sub(r"\x1b\[[0-9;]*m", "", out)
+    blocks = re.findall(r"Thread\s+0 finished image\s+(\d+)\n\s+Copy:\s+([\d.]+) ms\n\s+Kernel:\s+([\d.]+) ms\n"
+                        r"\s+Post Copy:\s+([\d.]+) ms\n\s+Post:\s+([\d.]+) ms\n\s+\S+\n\s+Total:\s+([\d.]+) ms "
+                        r"\(([\d.]+) GBps\)\n\s+(\d+) strong pixels\n\s+(\d+) filtered reflections \((\d+) pixels\)",
+                        plain)
+    assert sorted(int(b[0]) for b in blocks) == [0, 1, 2]
+    for b in blocks:
+        strong = oracle.dispersion(frames[int(b[0])], mask)
+        assert int(b[7]) == int(strong.sum())
+        assert float(b[5]) == pytest.approx(float(b[1]) + float(b[2]) + float(b[3]), abs=0.2)
+
+
+def test_devices_option_shards_stills_and_rotation(tmp_path):
+    """--devices: several contexts inside one process, frames sharded frame by frame (stills) or in
+    contiguous slabs merged through their boundary planes (rotation).  Listing device 0 three times
+    exercises the whole multi-context path on a one-GPU box; the results must not change."""
+    g = synth.small_geometry(240, 180)
+    mask = synth.make_mask(g)
+    stills = tmp_path / "stills"
+    stills.mkdir()
+    frames = synth.make_frames(g, mask, 7, np.uint16, config=8, n_spots=10)
+    write_stream(stills, frames, mask, 16)
+    rc, lines, out, err = run("spotfinder", [str(stills), "--threads", "4", "--devices", "0,0,0"])
+    assert rc == 0 and err == "" and sorted(l["file-number"] for l in lines) == list(range(7))
+    for l in lines:
+        strong = oracle.dispersion(frames[l["file-number"]], mask)
+        assert l["num_strong_pixels"] == int(strong.sum())
+    rot = tmp_path / "rot"
+    rot.mkdir()
+    sweep = synth.make_sweep(g, mask, 10, np.uint16, n_reflections=50)
+    write_stream(rot, sweep, mask, 16, omega_increment=0.1)
+    strong = np.stack([oracle.dispersion(f, mask) for f in sweep])
+    _, spots = oracle.connected_components(strong, sweep, want_labels=False)
+    kept, _, _ = oracle.filter_spots(spots, 3, 2.0)
+    texts = {}
+    for name, extra in (("one", []), ("three", ["--devices", "0-0,0,0"])):
+        outdir = tmp_path / name
+        outdir.mkdir()
+        rc, lines, out, err = run("spotfinder", [str(rot), "--threads", "3", "--writeout", *extra], cwd=outdir)
+        assert rc == 0 and err == "" and len(lines) == 10
+        assert int(re.search(r"Calculated\s+(\d+)\s+spots", out).group(1)) == len(spots)
+        assert int(re.search(r"Found\s+(\d+)\s+spots", out).group(1)) == len(kept)
+        texts[name] = (outdir / "3d_reflections.txt").read_text()
+        sig = re.search(r"Estimated sigma_b \(degrees\): ([0-9.]+)", out).group(1)
+        texts[name + "_sigma"] = sig
+    # the reference's text format and order (spotfinder.cc:1119-1148; tests/3d_connected_components.sh:55-64)
+    assert texts["one"].splitlines() == oracle.format_reflections_3d(kept)
+    assert texts["three"] == texts["one"]
+    assert texts["three_sigma"] == texts["one_sigma"]

@@ -7,8 +7,9 @@ frame slabs per GPU, boundary-plane label merge over torch.distributed (NCCL on 
 
 Every rank synthesises ONLY its slab (8 Poisson background frames cycled, the sweep's
 reflections stamped on top with a Gaussian rocking curve), streams it through the pinned ring
-with sweep recording on, labels the slab on its GPU (ffs_sweep_finish), and all ranks exchange
-{spots, exact sums, second moments, boundary planes} and merge (ffs_b200/sweep.py).  Prints one
+with sweep recording on, labels the slab on its GPU (ffs_sweep_finish), and the slabs are merged
+natively over NCCL (ffs_sweep_merge: boundary planes by ncclSend/ncclRecv, boundary-component
+records by ncclAllGather, csrc/api_multi.inl).  Prints one
 JSON line: frames, spots, and the time of each phase (max over ranks).  Host-side frame
 synthesis is inside `stream_s` (it is the slow part of that phase and is reported separately as
 `synth_s`); `finish_s` + `merge_s` are the 3D labelling itself.  --check re-runs the whole sweep
@@ -28,17 +29,18 @@ import torch.distributed as dist
 
 from ffs_b200 import synth
 from ffs_b200.spotfinder import Spotfinder
-from ffs_b200.sweep import gather_and_merge, merge_slabs, slab_bounds, slab_result_from
+from ffs_b200.sweep import NcclComm, merge_native, merge_slabs_native, slab_bounds, slab_result_from
 
 
 class SweepSource:
     """Deterministic frames of a rotation sweep, any frame on demand."""
 
-    def __init__(self, geom, mask, n_frames, dtype, n_bg=8):
+    def __init__(self, geom, mask, n_frames, dtype, n_bg=8, n_refl=None):
         self.g, self.mask, self.n, self.dtype = geom, mask, n_frames, dtype
         self.bg = [synth.make_frame(geom, mask, dtype, 4, k, background=2.0, n_hot=0, n_spots=0) for k in range(n_bg)]
         rng = np.random.Generator(np.random.PCG64(424242))
-        n_refl = max(8, int(round(40000 * (n_frames / 3600) * geom.pixels / synth.EIGER2_16M.pixels)))
+        if n_refl is None:
+            n_refl = max(8, int(round(40000 * (n_frames / 3600) * geom.pixels / synth.EIGER2_16M.pixels)))
         self.rx = rng.uniform(8, geom.width - 8, n_refl)
         self.ry = rng.uniform(8, geom.height - 8, n_refl)
         self.rz = rng.uniform(0, n_frames, n_refl)
@@ -111,19 +113,23 @@ def main():
     src = SweepSource(geom, mask, a.frames, np.uint16)
     z0, z1 = slab_bounds(a.frames, world, rank)
     times = {}
+    comm = NcclComm.from_torch(local) if world > 1 else None
     with Spotfinder(geom.width, geom.height, np.uint16, mask, n_slots=6, device=local) as sf:
         slab = run_slab(sf, src, z0, z1, times)
         if world > 1:
             dist.barrier()
         tm = time.perf_counter()
-        merged = gather_and_merge(slab, geom.width, geom.height)
+        if comm is not None:
+            merged, times["exchange_s"] = merge_native(sf, comm, z0, z1 - z0, slab.spots, gather=True)
+        else:
+            merged, times["exchange_s"] = merge_slabs_native([slab], geom.width, geom.height), 0.0
         times["merge_s"] = time.perf_counter() - tm
         kept, rs, rp = sf.filter_spots(merged, 3, 2.0)
         ok = None
         if a.check and rank == 0:
             t = {}
             whole = run_slab(sf, src, 0, a.frames, t)
-            ref = merge_slabs([whole], geom.width, geom.height)
+            ref = merge_slabs_native([whole], geom.width, geom.height)
             ok = bool(len(ref) == len(merged) and np.array_equal(ref["label"], merged["label"])
                       and np.array_equal(ref["num_pixels"], merged["num_pixels"])
                       and np.array_equal(ref["sum_intensity"], merged["sum_intensity"])
@@ -143,7 +149,8 @@ def main():
             "frames": a.frames, "n_gpus": world, "slab_components_total": int(sm[4].item()),
             "components_after_merge": int(len(merged)), "spots_after_filters": int(len(kept)),
             "stream_s": round(mx[0].item(), 3), "synth_s_inside_stream": round(mx[1].item(), 3),
-            "finish_3d_s": round(mx[2].item(), 3), "merge_s": round(mx[3].item(), 3),
+            "finish_3d_s": round(mx[2].item(), 3), "merge_s": round(mx[3].item(), 4),
+            "merge": "native: ncclSend/ncclRecv of boundary planes + ncclAllGather of boundary-component records",
             "labelling_frames_per_s": round(a.frames / (mx[2].item() + mx[3].item()), 1),
             "identical_to_single_gpu": ok}))
     if world > 1:
