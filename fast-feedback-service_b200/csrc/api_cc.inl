@@ -8,13 +8,10 @@ static int cc_setup(ffs_ctx* c) {
                       ? p.max_strong_per_frame
                       : (uint32_t)std::min<size_t>(std::max<size_t>(px / 16, 65536), 1u << 20);
     c->cap_spots = p.max_spots_per_frame ? p.max_spots_per_frame : std::max<uint32_t>(c->cap_strong / 4, 1024);
-    const int n_words = (int)(c->bits_pitch / 4) * (int)p.height;
-    c->n_chunks = (n_words + kChunkWords - 1) / kChunkWords;
     FFS_CK(c, cudaMalloc(&c->d_px_index, sizeof(uint32_t) * c->cap_strong * S));
     FFS_CK(c, cudaMalloc(&c->d_px_value, sizeof(uint32_t) * c->cap_strong * S));
     FFS_CK(c, cudaMalloc(&c->d_px_parent, sizeof(uint32_t) * c->cap_strong * S));
     FFS_CK(c, cudaMalloc(&c->d_acc, sizeof(SpotAcc) * c->cap_strong * S));
-    FFS_CK(c, cudaMalloc(&c->d_chunk_count, sizeof(uint32_t) * c->n_chunks * S));
     FFS_CK(c, cudaMalloc(&c->d_spots, sizeof(ffs_spot) * c->cap_spots * S));
     FFS_CK(c, cudaMalloc(&c->d_frame_counts, sizeof(uint32_t) * CNT_N * S));
     FFS_CK(c, cudaMemset(c->d_frame_counts, 0, sizeof(uint32_t) * CNT_N * S));
@@ -26,7 +23,6 @@ static void cc_teardown(ffs_ctx* c) {
     cudaFree(c->d_px_value);
     cudaFree(c->d_px_parent);
     cudaFree(c->d_acc);
-    cudaFree(c->d_chunk_count);
     cudaFree(c->d_spots);
     cudaFree(c->d_frame_counts);
 }
@@ -38,7 +34,7 @@ static void fill_cc_args(ffs_ctx* c, CCArgs& a, int first_slot, int n) {
     a.slot0 = first_slot;
     a.strong_bits = reinterpret_cast<const uint32_t*>(c->d_strong);
     a.bits_pitch = c->bits_pitch;
-    a.bits_stride = c->bits_stride;
+    a.bits_stride = c->zstride;  // strong planes live in the per-slot zero region
     a.image = c->d_frames;
     a.pitch = c->pitch;
     a.frame_stride = c->frame_stride;
@@ -52,6 +48,7 @@ static void fill_cc_args(ffs_ctx* c, CCArgs& a, int first_slot, int n) {
     a.parent = c->d_px_parent;
     a.acc = c->d_acc;
     a.chunk_count = c->d_chunk_count;
+    a.chunk_stride = c->zstride / 4;
     a.counts = c->d_frame_counts;
     a.spots = c->d_spots;
     a.cap_spots = c->cap_spots;

@@ -52,7 +52,7 @@ static int repack_mask(ffs_ctx* c) {
         const long long groups = (long long)((c->p.width + 7) / 8) * c->p.height;
         group_info_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, c->stream>>>(
           c->d_valid_bits, c->bits_pitch, (int)c->p.width, (int)c->p.height, c->d_info, c->info_pitch,
-          c->d_mcount, c->m_pitch);
+          c->d_mcount, c->m_pitch, c->d_info4, c->info4_pitch);
         c->launches++;
     }
     unsigned long long n = 0;
@@ -98,28 +98,37 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
     c->info_pitch = round_up(2 * (size_t)((p.width + 7) / 8), 16);
     FFS_CK(c, cudaMalloc(&c->d_info, c->info_pitch * p.height));
     FFS_CK(c, cudaMemset(c->d_info, 0, c->info_pitch * p.height));
+    c->info4_pitch = round_up(4 * (size_t)((p.width + 7) / 8), 16);
+    FFS_CK(c, cudaMalloc(&c->d_info4, c->info4_pitch * p.height));
+    FFS_CK(c, cudaMemset(c->d_info4, 0, c->info4_pitch * p.height));
     c->m_pitch = round_up(8 * (size_t)((p.width + 7) / 8), 16);
     FFS_CK(c, cudaMalloc(&c->d_mcount, c->m_pitch * p.height));
     FFS_CK(c, cudaMemset(c->d_mcount, 0, c->m_pitch * p.height));
     FFS_CK(c, cudaMalloc(&c->d_frames, c->frame_stride * S));
-    FFS_CK(c, cudaMalloc(&c->d_strong, c->bits_stride * S));
-    FFS_CK(c, cudaMalloc(&c->d_strong_count, sizeof(unsigned) * S * 3));
-    c->d_cand_count = c->d_strong_count + S;
-    c->d_ext_count = c->d_strong_count + 2 * S;
-    FFS_CK(c, cudaMemset(c->d_strong_count, 0, sizeof(unsigned) * S * 3));
+    {
+        const int n_words = (int)(c->bits_pitch / 4) * (int)p.height;
+        c->n_chunks = (n_words + kChunkWords - 1) / kChunkWords;
+        const size_t chunk_bytes = round_up(sizeof(uint32_t) * c->n_chunks, 16);
+        c->zstride = round_up(c->bits_stride + chunk_bytes + 4 * sizeof(unsigned), 256);
+        FFS_CK(c, cudaMalloc(&c->d_zero, c->zstride * S));
+        FFS_CK(c, cudaMemset(c->d_zero, 0, c->zstride * S));
+        c->d_strong = c->d_zero;
+        c->d_chunk_count = reinterpret_cast<uint32_t*>(c->d_zero + c->bits_stride);
+        c->d_strong_count = reinterpret_cast<unsigned*>(c->d_zero + c->bits_stride + chunk_bytes);
+        c->d_cand_count = c->d_strong_count + 1;
+        c->d_ext_count = c->d_strong_count + 2;
+        c->d_bad_count = c->d_strong_count + 3;
+    }
     if (p.trusted_max > 0 && (uint64_t)p.trusted_max < (p.bytes_per_pixel == 2 ? 0xffffull : 0xffffffffull)) {
         c->trusted_on = true;
         c->tmax = (uint32_t)p.trusted_max;
         c->vlim = std::min<uint32_t>(c->tmax, (1u << 24) - 1u);
         FFS_CK(c, cudaMalloc(&c->d_bad, sizeof(uint32_t) * (size_t)c->bad_cap * S));
-        FFS_CK(c, cudaMalloc(&c->d_bad_count, sizeof(unsigned) * S));
-        FFS_CK(c, cudaMemset(c->d_bad_count, 0, sizeof(unsigned) * S));
     }
     c->cand_cap = env_int("FFS_CAND_CAP", (int)std::max<size_t>(px / 8, 4096));
     FFS_CK(c, cudaMalloc(&c->d_cand, sizeof(uint32_t) * (size_t)c->cand_cap * S));
     FFS_CK(c, cudaMalloc(&c->d_valid_count, sizeof(unsigned long long)));
     FFS_CK(c, cudaMemset(c->d_frames, 0, c->frame_stride * S));
-    FFS_CK(c, cudaMemset(c->d_strong, 0, c->bits_stride * S));
     if (p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) {
         FFS_CK(c, cudaMalloc(&c->d_ext1, c->bits_stride * S));
         FFS_CK(c, cudaMalloc(&c->d_ext2, c->bits_stride * S));
@@ -159,10 +168,10 @@ static int create_impl(ffs_ctx* c, const uint8_t* mask) {
         cuuint32_t ibox[2] = {(cuuint32_t)FusedGeo<uint16_t>::INFO_ROW_BYTES, (cuuint32_t)FusedGeo<uint16_t>::SR};
         rc = make_tensor_map(c, &c->tm_info, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_info, idims, istrides, ibox);
         if (rc) return rc;
-        cuuint64_t mdims[2] = {(cuuint64_t)(c->m_pitch / 2), p.height};
-        cuuint64_t mstrides[1] = {c->m_pitch};
-        cuuint32_t mbox[2] = {(cuuint32_t)(ExtGeo<uint16_t>::M_ROW_BYTES / 2), 4};
-        rc = make_tensor_map(c, &c->tm_m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, c->d_mcount, mdims, mstrides, mbox);
+        cuuint64_t i4dims[2] = {4 * (cuuint64_t)((p.width + 7) / 8), p.height};
+        cuuint64_t i4strides[1] = {c->info4_pitch};
+        cuuint32_t i4box[2] = {(cuuint32_t)ExtGeo<uint16_t>::INFO4_ROW_BYTES, 4};
+        rc = make_tensor_map(c, &c->tm_info4, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, c->d_info4, i4dims, i4strides, i4box);
         if (rc) return rc;
         c->have_tm = true;
     }
@@ -208,15 +217,14 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_valid_bits);
     cudaFree(c->d_info);
     cudaFree(c->d_mcount);
+    cudaFree(c->d_info4);
     cudaFree(c->d_gain);
     cudaFree(c->d_frames);
-    cudaFree(c->d_strong);
+    cudaFree(c->d_zero);
     cudaFree(c->d_ext1);
     cudaFree(c->d_ext2);
-    cudaFree(c->d_strong_count);
     cudaFree(c->d_cand);
     cudaFree(c->d_bad);
-    cudaFree(c->d_bad_count);
     cudaFree(c->d_valid_count);
     for (auto& ev : c->prof_events) {
         cudaEventDestroy(ev.first);
@@ -364,7 +372,8 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.valid_frame_stride = 0;
     a.strong_bits = reinterpret_cast<uint32_t*>(c->d_strong);
     a.strong_pitch = c->bits_pitch;
-    a.strong_frame_stride = c->bits_stride;
+    a.strong_frame_stride = c->zstride;
+    a.zstride_words = c->zstride / 4;
     a.strong_count = c->d_strong_count;
     a.cand = c->d_cand;
     a.cand_count = c->d_cand_count;
@@ -390,7 +399,7 @@ static void fill_thresh_args(ffs_ctx* c, ThreshArgs& a, int first_slot, int n) {
     a.tmax = c->tmax;
     a.vlim = c->vlim;
     a.bad = c->d_bad;
-    a.bad_count = c->d_bad_count;
+    a.bad_count = c->trusted_on ? c->d_bad_count : nullptr;
     a.bad_cap = c->bad_cap;
 }
 
@@ -459,6 +468,49 @@ static int launch_dispersion(ffs_ctx* c, int first_slot, int n, cudaStream_t st)
     return FFS_OK;
 }
 
+// Rows per warp task of the streaming kernels (R + 6 a multiple of the 4-row stage depth).
+// Start from "as large as possible while every resident warp still gets ~2 tasks"; then, because
+// the last, partly filled wave of CTAs is idle time, prefer the tile height whose wave count sits
+// just below an integer, weighted by the 6 halo rows a tile re-reads (measured on a 32-frame
+// Eiger2 16M batch, tools/tile_sweep.sh: 12 row tiles = 2.92 waves 23.4 us/frame, 18 tiles = 4.38
+// waves 24.2).  A single frame -- the streaming path -- was ~1.3 waves under the first rule and
+// its second, nearly empty wave doubled the kernel time; one full wave of taller tiles does not.
+static int pick_wave_tile_rows(const ffs_ctx* c, int n, int n_strips, int height, int warps_per_cta,
+                               int ctas_per_sm, int resident_warps_per_sm) {
+    const int forced = env_int("FFS_TILE_ROWS", 0);
+    if (forced > 0) return std::min(forced, 500);
+    const long long want = 2LL * c->sm_count * resident_warps_per_sm;
+    int best = 4 * 8 - 6;
+    for (int groups = 64; groups >= 8; groups -= 2) {
+        best = groups * 4 - 6;
+        const long long tasks = (long long)n * n_strips * ((height + best - 1) / best);
+        if (tasks >= want) break;
+    }
+    const double slots = (double)c->sm_count * std::max(1, ctas_per_sm);
+    auto waves_of = [&](int rows) {
+        const long long t = (long long)n * n_strips * ((height + rows - 1) / rows);
+        return (double)((t + warps_per_cta - 1) / warps_per_cta) / slots;
+    };
+    static const int one_wave = env_int("FFS_ONE_WAVE", 1);
+    if (waves_of(best) > 1.5 || one_wave) {
+        double best_score = 0.0;
+        for (int groups = 129; groups >= 6; groups -= 1) {  // rows <= 510: queue entries hold 9-bit row offsets
+            const int rows = groups * 4 - 6;
+            const double w = waves_of(rows);
+            if (w < (one_wave ? 0.85 : 1.5)) continue;
+            const double score = w / std::ceil(w) * rows / (rows + 6.0);
+            if (score > best_score + 1e-9) {
+                best_score = score;
+                best = rows;
+            }
+        }
+        // same number of row tiles, split evenly (R + 6 still a multiple of the stage depth)
+        const int tiles = (height + best - 1) / best;
+        best = ((height + tiles - 1) / tiles + 6 + 3) / 4 * 4 - 6;
+    }
+    return best;
+}
+
 // The one-kernel path (dispersion_fused.cuh): TMA streaming + in-kernel exact resolution.
 template <typename PixelT, int kWarps, int kStages>
 static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
@@ -480,44 +532,8 @@ static int launch_fused_w(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
     static const int dbg = env_int("FFS_FUSED_DEBUG", 0);
     a.force_brute = dbg;  // 2: queue but do not resolve (timing experiments only)
-    {   // rows per warp task: R + 6 a multiple of the stage depth, as large as possible while
-        // every SM's resident warps still get ~2 tasks each
-        const int forced = env_int("FFS_TILE_ROWS", 0);
-        const int resident = std::max(1, (int)(200 * 1024 / G::smem_per_warp(kStages)));
-        const long long want = 2LL * c->sm_count * resident;
-        int best = 4 * 8 - 6;
-        for (int groups = 64; groups >= 8; groups -= 2) {
-            best = groups * 4 - 6;
-            const long long tasks = (long long)n * a.n_strips * ((a.height + best - 1) / best);
-            if (tasks >= want) break;
-        }
-        // Several waves of CTAs (a batch of frames): the last, partly filled wave is idle time, so
-        // prefer the tile height whose wave count sits just below an integer, weighted by the
-        // halo rows a tile re-reads (measured on a 32-frame Eiger2 16M batch, tools/tile_sweep.sh:
-        // 12 row tiles = 2.92 waves 23.4 us/frame, 18 tiles = 4.38 waves 24.2)
-        const double slots = (double)c->sm_count * (G::MIN_WARPS_PER_SM / kWarps);
-        auto waves_of = [&](int rows) {
-            const long long t = (long long)n * a.n_strips * ((a.height + rows - 1) / rows);
-            return (double)((t + kWarps - 1) / kWarps) / slots;
-        };
-        if (waves_of(best) > 1.5) {
-            double best_score = 0.0;
-            for (int groups = 124; groups >= 16; groups -= 1) {
-                const int rows = groups * 4 - 6;
-                const double w = waves_of(rows);
-                if (w < 1.5) continue;
-                const double score = w / std::ceil(w) * rows / (rows + 6.0);
-                if (score > best_score + 1e-9) {
-                    best_score = score;
-                    best = rows;
-                }
-            }
-            // same number of row tiles, split evenly (R + 6 still a multiple of the stage depth)
-            const int tiles = (a.height + best - 1) / best;
-            best = ((a.height + tiles - 1) / tiles + 6 + 3) / 4 * 4 - 6;
-        }
-        a.tile_rows = forced > 0 ? std::min(forced, 500) : best;
-    }
+    a.tile_rows = pick_wave_tile_rows(c, n, a.n_strips, a.height, kWarps, G::MIN_WARPS_PER_SM / kWarps,
+                                      std::max(1, (int)(200 * 1024 / G::smem_per_warp(kStages))));
     a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
     const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
     const unsigned grid = (unsigned)((tasks + kWarps - 1) / kWarps);
@@ -555,13 +571,8 @@ static int launch_fused(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
 }
 
 static int threshold_impl(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
-    FFS_CK(c, cudaMemsetAsync(c->d_strong + (size_t)first_slot * c->bits_stride, 0,
-                              c->bits_stride * n, st));
-    FFS_CK(c, cudaMemsetAsync(c->d_strong_count + first_slot, 0, sizeof(unsigned) * n, st));
-    FFS_CK(c, cudaMemsetAsync(c->d_cand_count + first_slot, 0, sizeof(unsigned) * n, st));
-    FFS_CK(c, cudaMemsetAsync(c->d_chunk_count + (size_t)first_slot * c->n_chunks, 0,
-                              sizeof(uint32_t) * c->n_chunks * n, st));
-    if (c->trusted_on) FFS_CK(c, cudaMemsetAsync(c->d_bad_count + first_slot, 0, sizeof(unsigned) * n, st));
+    // strong planes, chunk counts and counters of the batch: one memset (they share a per-slot region)
+    FFS_CK(c, cudaMemsetAsync(c->d_zero + (size_t)first_slot * c->zstride, 0, c->zstride * n, st));
     if (c->p.algorithm == FFS_ALGO_DISPERSION_EXTENDED) return extended_impl(c, first_slot, n, st);
     static const int two_kernel = env_int("FFS_TWO_KERNEL", 0);  // A/B: the round-1 prefilter + resolve pair
     if (two_kernel || env_int("FFS_FORCE_BRUTE", 0) || c->gain_brute || trusted_needs_brute(c)) {
@@ -614,12 +625,12 @@ static int get_u8_plane(ffs_ctx* c, const uint8_t* d_plane, uint8_t* out) {
 
 extern "C" int ffs_get_strong_bits(ffs_ctx* c, int slot, uint8_t* out) {
     if (!slots_ok(c, slot, 1) || !out) return FFS_ERR_ARG;
-    return get_bits_plane(c, c->d_strong + (size_t)slot * c->bits_stride, out);
+    return get_bits_plane(c, c->d_strong + (size_t)slot * c->zstride, out);
 }
 
 extern "C" int ffs_get_strong_u8(ffs_ctx* c, int slot, uint8_t* out) {
     if (!slots_ok(c, slot, 1) || !out) return FFS_ERR_ARG;
-    return get_u8_plane(c, c->d_strong + (size_t)slot * c->bits_stride, out);
+    return get_u8_plane(c, c->d_strong + (size_t)slot * c->zstride, out);
 }
 
 extern "C" int ffs_get_extended_stage_u8(ffs_ctx* c, int slot, int stage, uint8_t* out) {

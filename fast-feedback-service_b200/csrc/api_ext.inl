@@ -1,6 +1,37 @@
 // api_ext.inl -- dispersion_extended launch sequence (see extended.cuh).
 static int extended_setup(ffs_ctx*) { return FFS_OK; }
 
+template <typename PixelT, int kWarps>
+static int launch_ext_pass1(ffs_ctx* c, ThreshArgs& a, int n, cudaStream_t st) {
+    using G = FusedGeo<PixelT>;
+    using E = ExtGeo<PixelT>;
+    constexpr int kStages = 2;
+    auto kern = ext_pass1_kernel<PixelT, kStages, kWarps>;
+    const int smem = kWarps * E::smem_per_warp(kStages) + 128;
+    static bool attr_done[64] = {};
+    if (!attr_done[c->p.device & 63]) {
+        FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       (int)cudaSharedmemCarveoutMaxShared));
+        attr_done[c->p.device & 63] = true;
+    }
+    a.force_brute = 0;
+    a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
+    static int ctas_per_sm[64] = {};
+    if (!ctas_per_sm[c->p.device & 63]) {
+        int nb = 0;
+        FFS_CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, kWarps * 32, smem));
+        ctas_per_sm[c->p.device & 63] = std::max(1, nb);
+    }
+    a.tile_rows = pick_wave_tile_rows(c, n, a.n_strips, a.height, kWarps, ctas_per_sm[c->p.device & 63],
+                                      std::max(1, (int)(200 * 1024 / E::smem_per_warp(kStages))));
+    a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
+    const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
+    kern<<<(unsigned)((tasks + kWarps - 1) / kWarps), kWarps * 32, smem, st>>>(c->tm_img8, c->tm_info4, a);
+    FFS_CK(c, cudaGetLastError());
+    return FFS_OK;
+}
+
 template <typename PixelT>
 static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     // threshold_impl has already zeroed the strong planes, strong counters and candidate counters
@@ -10,6 +41,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     ThreshArgs a{};
     fill_thresh_args(c, a, first_slot, n);
     a.strong_bits = reinterpret_cast<uint32_t*>(c->d_ext1);
+    a.strong_frame_stride = c->bits_stride;  // the D planes are a plain array of bit-planes
     a.strong_count = c->d_ext_count;
     a.chunk_count = nullptr;  // the D plane is not the connected-components input
     static const int brute = env_int("FFS_EXT_BRUTE", 0);  // A/B: resolve every pixel exactly
@@ -20,30 +52,14 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
         a.force_brute = 1;
         resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
     } else {
-        // streaming first pass (extended_stream.cuh)
-        using G = FusedGeo<PixelT>;
-        using E = ExtGeo<PixelT>;
-        constexpr int kStages = 2, kWarps = 3;
-        auto kern = ext_pass1_kernel<PixelT, kStages, kWarps>;
-        const int smem = kWarps * E::smem_per_warp(kStages) + 128;
-        static bool attr_done[64] = {};
-        if (!attr_done[c->p.device & 63]) {
-            FFS_CK(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            attr_done[c->p.device & 63] = true;
-        }
-        a.force_brute = 0;
-        a.n_strips = (a.width + G::OUT_COLS - 1) / G::OUT_COLS;
-        const int resident = std::max(1, (int)(200 * 1024 / E::smem_per_warp(kStages)));
-        const long long want = 2LL * c->sm_count * resident;
-        int best = 4 * 8 - 6;
-        for (int groups = 64; groups >= 8; groups -= 2) {
-            best = groups * 4 - 6;
-            if ((long long)n * a.n_strips * ((a.height + best - 1) / best) >= want) break;
-        }
-        a.tile_rows = best;
-        a.n_row_tiles = (a.height + a.tile_rows - 1) / a.tile_rows;
-        const long long tasks = (long long)n * a.n_strips * a.n_row_tiles;
-        kern<<<(unsigned)((tasks + kWarps - 1) / kWarps), kWarps * 32, smem, st>>>(c->tm_img8, c->tm_info, c->tm_m, a);
+        // streaming first pass (extended_stream.cuh).  Warps are independent tasks; their number per CTA
+        // only decides how the per-warp shared memory (11 KB) packs into an SM: 10 per CTA -> 2 CTAs =
+        // 20 resident warps (3 per CTA: 18, 4: 16).
+        static const int ext_warps = env_int("FFS_EXT_WARPS", 10);
+        int rc = ext_warps == 3   ? launch_ext_pass1<PixelT, 3>(c, a, n, st)
+                 : ext_warps == 4 ? launch_ext_pass1<PixelT, 4>(c, a, n, st)
+                                  : launch_ext_pass1<PixelT, 10>(c, a, n, st);
+        if (rc) return rc;
     }
     // erosion -> B plane (validity of the second pass) + list of core pixels
     ErodeArgs e{};
@@ -59,6 +75,7 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     e.cand = c->d_cand;
     e.cand_count = c->d_cand_count;
     e.cand_cap = c->cand_cap;
+    e.zstride_words = c->zstride / 4;
     erode_kernel<<<dim3((unsigned)(c->sm_count * 2), (unsigned)n), 256, 0, st>>>(e);
     // final pass over the core pixels: 11x11 window over B-valid pixels
     ThreshArgs f{};

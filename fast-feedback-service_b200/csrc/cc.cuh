@@ -54,7 +54,8 @@ struct CCArgs {
     uint32_t* px_value;           // [slot][cap]
     uint32_t* parent;             // [slot][cap]
     SpotAcc* acc;                 // [slot][cap]
-    uint32_t* chunk_count;        // [slot][n_chunks]  counts, then exclusive offsets
+    uint32_t* chunk_count;        // slot z at + z * chunk_stride: counts, then exclusive offsets
+    size_t chunk_stride;          // uint32 units (the per-slot zero region, context.cuh d_zero)
     uint32_t* counts;             // [slot][CNT_N]
     ffs_spot* spots;              // [slot][cap_spots]
     uint32_t cap_spots;

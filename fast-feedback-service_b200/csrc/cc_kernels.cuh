@@ -24,14 +24,14 @@ __global__ void __launch_bounds__(256) cc_count_kernel(const CCArgs a) {
     if (threadIdx.x == 0) {
         uint32_t t = 0;
         for (int w = 0; w < 8; ++w) t += ws[w];
-        a.chunk_count[(size_t)z * a.n_chunks + blockIdx.x] = t;
+        a.chunk_count[(size_t)z * a.chunk_stride + blockIdx.x] = t;
     }
 }
 
 // K2: exclusive scan of the chunk counts of one frame.  grid (n_frames), 256 threads.
 __global__ void __launch_bounds__(256) cc_scan_kernel(const CCArgs a) {
     const int z = a.slot0 + blockIdx.x;
-    uint32_t* cc = a.chunk_count + (size_t)z * a.n_chunks;
+    uint32_t* cc = a.chunk_count + (size_t)z * a.chunk_stride;
     uint32_t running = 0;
     for (int base = 0; base < a.n_chunks; base += 256) {
         const int k = base + threadIdx.x;
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(256) cc_extract_kernel(const CCArgs a) {
     uint32_t tot;
     uint32_t off = block_exclusive_scan_256(c, &tot);
     if (tot == 0) return;
-    off += a.chunk_count[(size_t)z * a.n_chunks + blockIdx.x];
+    off += a.chunk_count[(size_t)z * a.chunk_stride + blockIdx.x];
     uint32_t* idx = a.px_index + (size_t)z * a.cap;
     uint32_t* val = a.px_value + (size_t)z * a.cap;
     uint32_t* par = a.parent + (size_t)z * a.cap;

@@ -98,7 +98,9 @@
     const auto all_images_start = clk::now();
     printf("Finding spots in %u images (%u x %u) with %u threads\n", num_images, width, height, args.threads);
 
-    const bool host_decode = getenv("FFS_HOST_DECODE") && atoi(getenv("FFS_HOST_DECODE")) != 0;
+    // developer knob (honoured only with FFS_DEV_KNOBS=1, like the library's): decode chunks on the host
+    const bool host_decode = getenv("FFS_DEV_KNOBS") && atoi(getenv("FFS_DEV_KNOBS")) != 0 &&
+                             getenv("FFS_HOST_DECODE") && atoi(getenv("FFS_HOST_DECODE")) != 0;
     auto worker = [&](int thread_id) {
         std::vector<uint8_t> chunk, scratch;
         while (!g_stop) {

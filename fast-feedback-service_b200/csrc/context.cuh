@@ -62,10 +62,16 @@ struct ffs_ctx {
     double gain_min = 1.0;            // over the mask-valid pixels: scales the pruning bound
     double gain_max = 1.0;            // (extended first pass: bracket of the right-hand side)
     bool gain_brute = false;          // gain map with non-positive / non-finite entries: no pruning
+    uint8_t* d_info4 = nullptr;       // per group of 8 pixels: {validity byte, m_ub | full << 6, m_lb, 0} (extended_stream.cuh)
+    size_t info4_pitch = 0;
     uint8_t* d_mcount = nullptr;      // per pixel: valid pixels in its clipped 7x7 window (extended_stream.cuh)
     size_t m_pitch = 0;
     uint8_t* d_frames = nullptr;      // n_slots pitched frames
-    uint8_t* d_strong = nullptr;      // n_slots strong bit-planes
+    // Everything a frame's threshold must find zeroed sits in ONE region per slot, cleared by one
+    // memset per batch: [strong bit-plane | chunk counts | strong, cand, ext, bad counters]
+    uint8_t* d_zero = nullptr;        // n_slots * zstride bytes
+    size_t zstride = 0;               // bytes per slot region (multiple of 256)
+    uint8_t* d_strong = nullptr;      // = d_zero: slot z's strong bit-plane at + z * zstride
     uint8_t* d_ext1 = nullptr;        // extended: first-pass dispersion bit-planes
     uint8_t* d_ext2 = nullptr;        // extended: eroded validity bit-planes
     unsigned int* d_strong_count = nullptr;  // n_slots (+ n_slots candidate counters behind)
@@ -113,7 +119,7 @@ struct ffs_ctx {
     CUtensorMap tm_img{};     // 3D: x, y, slot
     CUtensorMap tm_valid{};   // 2D validity bytes
     CUtensorMap tm_info{};    // 2D group info bytes
-    CUtensorMap tm_m{};       // 2D per-pixel window counts, as u16 pairs
+    CUtensorMap tm_info4{};   // 2D 4-byte group info (extended first pass)
     CUtensorMap tm_img8{};    // 3D image, 256-pixel box (fused kernel; == tm_img for 16-bit pixels)
     CUtensorMap tm_valid2{};  // 3D eroded validity (extended second pass): x, y, slot
     bool have_tm = false;

@@ -91,7 +91,8 @@ struct FusedGeo {
 // image-clipped 7x7 window (standalone.cc:126-130 clipping).
 __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t bits_pitch, int width,
                                   int height, uint8_t* __restrict__ info, size_t info_pitch,
-                                  uint8_t* __restrict__ mplane, size_t m_pitch) {
+                                  uint8_t* __restrict__ mplane, size_t m_pitch,
+                                  uint8_t* __restrict__ info4, size_t info4_pitch) {
     const int groups = (width + 7) / 8;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (long long)groups * height) return;
@@ -121,6 +122,9 @@ __global__ void group_info_kernel(const uint8_t* __restrict__ valid_bits, size_t
     out[0] = (uint8_t)vb;
     // bit 6: every valid pixel of the group has a full window (inside the image, all 49 valid)
     out[1] = (uint8_t)(mub | (mlb == 49u ? 0x40u : 0u));
+    // 4-byte variant for the extended first pass (extended_stream.cuh): + the smallest count
+    *reinterpret_cast<uint32_t*>(info4 + (size_t)row * info4_pitch + 4 * gi) =
+      vb | ((mub | (mlb == 49u ? 0x40u : 0u)) << 8) | ((mlb & 63u) << 16);
     // per-pixel window counts (extended_stream.cuh): 8 bytes per group, 0 beyond the width
     uint2 mm;
     mm.x = m[0] | (m[1] << 8) | (m[2] << 16) | (m[3] << 24);
@@ -342,7 +346,7 @@ __device__ __noinline__ uint32_t fused_resolve(const ThreshArgs* __restrict__ ap
         pqn = pgn = 0;
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
-    if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
+    if (lane == 0 && found) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, found);
     return (uint32_t)qn | ((uint32_t)pqn << 8) | ((uint32_t)pgn << 20);
 }
 

@@ -28,6 +28,7 @@ struct ErodeArgs {
     uint32_t* cand;              // per slot: core pixels  col | row << 13
     unsigned int* cand_count;
     unsigned int cand_cap;
+    size_t zstride_words;        // counters of consecutive slots are this many uint32 apart
 };
 
 // One thread per 32-bit word of the plane.  grid (blocks, n_frames).
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(256) erode_kernel(const ErodeArgs a) {
                 if (lane >= off) incl += v;
             }
             uint32_t base = 0;
-            if (lane == 31) base = atomicAdd(a.cand_count + z, incl);
+            if (lane == 31) base = atomicAdd(a.cand_count + (size_t)z * a.zstride_words, incl);
             base = __shfl_sync(0xffffffffu, base, 31);
             uint32_t slot = base + incl - cnt;
             for (uint32_t bits = core; bits; bits &= bits - 1, ++slot) {
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(256) final_kernel(const ThreshArgs a, const ui
     const int z = a.slot0 + blockIdx.y;
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
     const uint8_t* bplane = a.valid_bits + (size_t)z * a.valid_frame_stride;
-    const unsigned n_cand = a.cand_count[z];
+    const unsigned n_cand = a.cand_count[(size_t)z * a.zstride_words];
     const bool brute = a.force_brute || n_cand > a.cand_cap;
     const long long total = brute ? (long long)a.width * a.height : (long long)n_cand;
     const uint32_t* list = a.cand + (size_t)z * a.cand_cap;
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(256) final_kernel(const ThreshArgs a, const ui
         }
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
-    if ((threadIdx.x & 31) == 0 && found) atomicAdd(a.strong_count + z, found);
+    if ((threadIdx.x & 31) == 0 && found) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, found);
 }
 
 }  // namespace ffsb

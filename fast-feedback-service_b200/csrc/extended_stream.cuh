@@ -14,7 +14,9 @@
 //       -- the outgoing row's squares are recomputed from the ring's packed values -- and
 //       7-tap sums from 6 shuffles;
 //   m : the number of mask-valid pixels in the clipped window is a property of the mask,
-//       precomputed per pixel (group_info_kernel) and TMA-loaded as a third tile.
+//       precomputed once (group_info_kernel): the largest and smallest count over each group's
+//       valid pixels travel in the 4-byte group info the TMA delivers beside the frame; the
+//       per-pixel counts are read from the (L2-resident) plane by the rows that need them.
 // The comparison  m*y - x^2 > x * K(m),  K(m) = m-1 + nsig_b*sqrt(2(m-1)),  is made in fp32 with
 // an explicit error bound; only pixels inside that bound, and windows that contain a pixel
 // above 1169 (or, for 32-bit data, an uncounted pixel >= 2^24), are queued and decided by the
@@ -23,6 +25,10 @@
 #pragma once
 #include "dispersion_fused.cuh"
 
+#ifndef EXT_ROW_UNROLL
+#define EXT_ROW_UNROLL 2  // rows of a stage unrolled together (4 = whole stage: more code, no faster)
+#endif
+
 namespace ffsb {
 
 template <typename PixelT>
@@ -30,10 +36,11 @@ struct ExtGeo {
     using F = FusedGeo<PixelT>;
     static constexpr int SR = 4;
     static constexpr unsigned CLAMP = 1169u;     // 49 * 1169^2 < 2^26
-    static constexpr int M_ROW_BYTES = 272;      // 256 per-pixel counts + 16 B of alignment lead-in
-    static constexpr int M_STAGE_BYTES = (SR * M_ROW_BYTES + 127) / 128 * 128;
-    static constexpr int STAGE_BYTES = F::IMG_STAGE_BYTES + F::INFO_STAGE_BYTES + M_STAGE_BYTES;
-    static constexpr int TX_BYTES = F::IMG_STAGE_BYTES + SR * F::INFO_ROW_BYTES + SR * M_ROW_BYTES;
+    // group info, 4 bytes per group {validity, m_ub | full << 6, m_lb, 0}: 32 groups + <= 12 B alignment slack
+    static constexpr int INFO4_ROW_BYTES = 144;
+    static constexpr int INFO4_STAGE_BYTES = (SR * INFO4_ROW_BYTES + 127) / 128 * 128;
+    static constexpr int STAGE_BYTES = F::IMG_STAGE_BYTES + INFO4_STAGE_BYTES;
+    static constexpr int TX_BYTES = F::IMG_STAGE_BYTES + SR * INFO4_ROW_BYTES;
     static constexpr int GQ_CAP = 64, PQ_CAP = 288;
     static constexpr int QUEUE_BYTES = (GQ_CAP + PQ_CAP) * 4;
     static_assert(QUEUE_BYTES % 128 == 0, "alignment");
@@ -100,28 +107,95 @@ __device__ __noinline__ uint32_t ext_resolve(const ThreshArgs* __restrict__ ap, 
         pqn = 0;
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
-    if (lane == 0 && found) atomicAdd(a.strong_count + z, found);
+    if (lane == 0 && found) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, found);
     return (uint32_t)qn | ((uint32_t)pqn << 8);
+}
+
+// A row that survived the integer prune (some lane holds a pixel whose test is not clearly false):
+// per-pixel fp32 comparison with an explicit error bound; pixels inside the bound, and windows
+// whose sums are not exact (flagged), go to the exact routine.  Out of line on purpose: inlined
+// into the four-row loop body it pushed the hot loop out of the instruction cache
+// (stall_no_instruction was the top stall reason, profiles/r2_ext_pass1_ncu_full.json).
+// state = qn | pqn << 8; returns {new state, D bits set by this lane}.
+template <typename PixelT>
+__device__ __noinline__ uint2 ext_row_slow(const ThreshArgs* __restrict__ ap, const float4* __restrict__ ktab,
+                                           uint32_t* gq, uint32_t state, uint4 hxa, uint4 hxb, uint4 hya, uint4 hyb,
+                                           uint32_t vb, uint32_t flags, int out_row, int group, int x0,
+                                           int r0, int z) {
+    const ThreshArgs& a = *ap;
+    // per-pixel window counts of this group's 8 pixels: a property of the mask (group_info_kernel),
+    // L2-resident across frames; only rows that reach this path read them
+    const uint2 mw = ((flags & 2u) && group < (int)(a.m_pitch >> 3)) ? *reinterpret_cast<const uint2*>(a.mcount + (size_t)out_row * a.m_pitch + 8 * (size_t)group)
+                                  : make_uint2(0u, 0u);
+    const int lane = threadIdx.x & 31;
+    const bool flagged = flags & 1u, out_lane = flags & 2u, store_lane = flags & 4u;
+    const uint32_t Hx[8] = {hxa.x, hxa.y, hxa.z, hxa.w, hxb.x, hxb.y, hxb.z, hxb.w};
+    const uint32_t Hy[8] = {hya.x, hya.y, hya.z, hya.w, hyb.x, hyb.y, hyb.z, hyb.w};
+    int qn = state & 0xff, pqn = state >> 8;
+    uint32_t dbits = 0, border = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t m = ((j < 4 ? mw.x : mw.y) >> (8 * (j & 3))) & 0xffu;
+        const float4 mk = ktab[m];
+        const float xf = (float)Hx[j], yf = (float)Hy[j];
+        const float t = mk.x * yf, uu = xf * xf, rhs_lo = xf * mk.y, rhs_hi = xf * mk.z;
+        const float lhs = t - uu;
+        const float sl = 4e-7f * (t + uu + rhs_hi);
+        const bool ok = ((vb >> j) & 1u) && (int)m >= a.min_count;
+        const bool hi = (lhs - sl) > rhs_hi, lo = (lhs + sl) > rhs_lo;
+        dbits |= (ok && hi) ? (1u << j) : 0u;
+        border |= (ok && lo && !hi) ? (1u << j) : 0u;
+    }
+    if (flagged) {  // sums are not exact here: decide every valid pixel exactly
+        dbits = 0;
+        border = vb;
+    }
+    uint8_t* dplane = reinterpret_cast<uint8_t*>(a.strong_bits) + (size_t)z * a.strong_frame_stride;
+    if (store_lane) dplane[(size_t)out_row * a.strong_pitch + group] = (uint8_t)dbits;
+    const bool push = out_lane && border != 0;
+    const unsigned ball = __ballot_sync(0xffffffffu, push);
+    if (ball) {
+        if (push)
+            gq[qn + __popc(ball & ((1u << lane) - 1u))] =
+              (uint32_t)lane | ((uint32_t)(out_row - r0) << 5) | (border << 14);
+        qn += __popc(ball);
+        __syncwarp();
+        if (qn >= 32) {
+            const uint32_t st2 = ext_resolve<PixelT>(ap, gq, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), 32, false);
+            qn = st2 & 0xff;
+            pqn = st2 >> 8;
+        }
+    }
+    return make_uint2((uint32_t)qn | ((uint32_t)pqn << 8), out_lane ? (uint32_t)__popc(dbits) : 0u);
 }
 
 template <typename PixelT, int STAGES, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
-  ext_pass1_kernel(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_info,
-                   const __grid_constant__ CUtensorMap tm_m, const __grid_constant__ ThreshArgs a) {
+  ext_pass1_kernel(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_info4,
+                   const __grid_constant__ ThreshArgs a) {
     using G = FusedGeo<PixelT>;
     using E = ExtGeo<PixelT>;
     constexpr int SR = 4, KH = 3, PPL = 8;
     constexpr uint32_t CL = E::CLAMP;
+    constexpr int kRowUnroll = EXT_ROW_UNROLL;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // {m, K(m)*g_lo, K(m)*g_hi},  K(m) = m-1 + nsig_b*sqrt(2(m-1)).  Without a gain map g_lo = g_hi = 1;
     // with one (baseline.cpp:536: c = gain*x*K(m)) the smallest / largest gain bracket the
     // right-hand side and the pixels in between are decided exactly.
     __shared__ float4 ktab[64];
+    // floor(K(m) * g_lo), rounded down with a margin: m*y - x^2 <= x * ktabi[m'] for some m' <= m
+    // proves a <= c, i.e. D = 0, in exact integer arithmetic (see the row prune below)
+    __shared__ uint32_t ktabi[64];
+    __shared__ ThreshArgs sa;  // the out-of-line paths read their arguments from here (see dispersion_fused.cuh)
+    for (int t = threadIdx.x; t < (int)(sizeof(ThreshArgs) / 4); t += WARPS * 32)
+        reinterpret_cast<uint32_t*>(&sa)[t] = reinterpret_cast<const uint32_t*>(&a)[t];
     for (int t = threadIdx.x; t < 64; t += WARPS * 32) {
         const float m1 = (float)max(t - 1, 0);
         const float k = m1 + (float)a.nsig_b * sqrtf(2.0f * m1);
         ktab[t] = make_float4((float)t, k * a.g_lo, k * a.g_hi, 0.f);
+        const double kd = ((double)max(t - 1, 0) + a.nsig_b * sqrt(2.0 * (double)max(t - 1, 0))) * (double)a.g_lo;
+        ktabi[t] = (uint32_t)floor(fmax(kd * (1.0 - 1e-6), 0.0));
     }
     __syncthreads();
 
@@ -147,9 +221,8 @@ __global__ void __launch_bounds__(WARPS * 32)
     const int n_groups = (n_load_rows + SR - 1) / SR;
     const int x0 = strip * G::OUT_COLS - PPL;
     const int y_first = r0 - KH;
-    const int info_b = 2 * (strip * G::OUT_LANES - 1);
+    const int info_b = 4 * (strip * G::OUT_LANES - 1);  // byte offset of lane 0's group in an info4 row
     const int info_b0 = info_b & ~15;
-    const int m_x = (x0 - 8) / 2;  // u16 units; x0 - 8 is a multiple of 16 (and may be negative)
 
     if (lane == 0) {
         for (int s = 0; s < STAGES; ++s) ptx::mbar_init(bars + s, 1);
@@ -165,31 +238,25 @@ __global__ void __launch_bounds__(WARPS * 32)
         uint8_t* dst = stage_base + s * E::STAGE_BYTES;
         ptx::mbar_arrive_expect_tx(bars + s, E::TX_BYTES);
         ptx::tma_load_3d(dst, &tm_img, bars + s, x0, y_first + g * SR, z);
-        ptx::tma_load_2d(dst + G::IMG_STAGE_BYTES, &tm_info, bars + s, info_b0, y_first + g * SR);
-        // the count tile is row-shifted: load-row i carries the counts of its centre row i-3
-        ptx::tma_load_2d(dst + G::IMG_STAGE_BYTES + G::INFO_STAGE_BYTES, &tm_m, bars + s, m_x,
-                         y_first + g * SR - KH);
+        ptx::tma_load_2d(dst + G::IMG_STAGE_BYTES, &tm_info4, bars + s, info_b0, y_first + g * SR);
     };
     if (lane == 0) {
         for (int g = 0; g < STAGES && g < n_groups; ++g) issue(g, g);
     }
 
     const bool out_lane = lane >= 1 && lane <= G::OUT_LANES;
-    const uint32_t lt_mask = (1u << lane) - 1u;
     const int group = strip * G::OUT_LANES + lane - 1;            // pixel group of this lane
     const bool store_lane = out_lane && group < (int)a.strong_pitch;
-    uint8_t* dplane = reinterpret_cast<uint8_t*>(a.strong_bits) + (size_t)z * a.strong_frame_stride;
     int qn = 0, pqn = 0;
     unsigned n_set = 0;
 
     uint32_t V[4] = {0, 0, 0, 0};                  // packed column sums of x over the last 7 rows
     uint32_t Vy[8] = {0, 0, 0, 0, 0, 0, 0, 0};     // column sums of the squares
     uint32_t big7 = 0;                             // bit r: row i-r of this lane holds a pixel > CLAMP
-    uint32_t hi1 = 0, hi2 = 0, hi3 = 0;            // validity bytes of rows i-1, i-2, i-3
+    uint32_t hi1 = 0, hi2 = 0, hi3 = 0;            // group info of rows i-1, i-2, i-3
     uint8_t* ring_lane = ring + lane * 16;
     const int pimg_off = lane * PPL * (int)sizeof(PixelT);
-    const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 2 * lane;
-    const int pm_off = G::IMG_STAGE_BYTES + G::INFO_STAGE_BYTES + 8 + 8 * lane;
+    const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 4 * lane;
 
     int s = 0;
     uint32_t phase = 0;
@@ -198,11 +265,11 @@ __global__ void __launch_bounds__(WARPS * 32)
         const uint8_t* st = stage_base + s * E::STAGE_BYTES;
         uint8_t* rcur = ring_lane + ((g & 1) ? SR * G::RING_ROW_BYTES : 0);
         uint8_t* roth = ring_lane + ((g & 1) ? 0 : SR * G::RING_ROW_BYTES);
-#pragma unroll
+#pragma unroll kRowUnroll
         for (int u = 0; u < SR; ++u) {
             const int i = g * SR + u;
             // ---- load, mask, clamp ------------------------------------------------------------
-            const uint32_t info = *reinterpret_cast<const uint16_t*>(st + pinfo_off + u * G::INFO_ROW_BYTES);
+            const uint32_t info = *reinterpret_cast<const uint32_t*>(st + pinfo_off + u * E::INFO4_ROW_BYTES);
             uint32_t c[4];
             bool big;
             if constexpr (sizeof(PixelT) == 2) {
@@ -285,44 +352,34 @@ __global__ void __launch_bounds__(WARPS * 32)
                 Hy[0] = Ey[0] + Ey[1] + Ey[2] + Ey[3] + Ey[4] + Ey[5] + Ey[6];
 #pragma unroll
                 for (int j = 1; j < 8; ++j) Hy[j] = Hy[j - 1] + Ey[j + 6] - Ey[j - 1];
-                // ---- per-pixel test in fp32 with an error bound --------------------------------------
-                const uint2 mw = *reinterpret_cast<const uint2*>(st + pm_off + u * E::M_ROW_BYTES);
+                // ---- row prune: on background the test fails by a wide margin for every pixel.  With
+                // m_hi >= m >= m_lo over the group's valid pixels (both in the 4-byte group info) and K increasing in m,
+                //     m_hi * y <= x * (x + floor(K(m_lo) g_lo))   ==>   m*y - x^2 <= x K(m) g   ==>   D = 0
+                // in exact 32-bit integers (m*y < 49 * 2^26, x (x + K) < 3.3e9).  Only when some lane of
+                // the warp has a pixel that survives does the row take the per-pixel fp32 path below;
+                // the D plane is pre-zeroed, so a pruned row stores nothing.
                 const uint32_t vb = hi3 & 0xffu;  // validity of the centre row's pixels
-                uint32_t dbits = 0, border = 0;
+                {
+                    const uint32_t m_hi = (hi3 >> 8) & 0x3fu, m_lo = (hi3 >> 16) & 0x3fu;
+                    const uint32_t kf = ktabi[m_lo];
+                    bool maybe = flagged;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint32_t m = ((j < 4 ? mw.x : mw.y) >> (8 * (j & 3))) & 0xffu;
-                    const float4 mk = ktab[m];
-                    const float xf = (float)Hx[j], yf = (float)Hy[j];
-                    const float t = mk.x * yf, uu = xf * xf, rhs_lo = xf * mk.y, rhs_hi = xf * mk.z;
-                    const float lhs = t - uu;
-                    const float sl = 4e-7f * (t + uu + rhs_hi);
-                    const bool ok = ((vb >> j) & 1u) && (int)m >= a.min_count;
-                    const bool hi = (lhs - sl) > rhs_hi, lo = (lhs + sl) > rhs_lo;
-                    dbits |= (ok && hi) ? (1u << j) : 0u;
-                    border |= (ok && lo && !hi) ? (1u << j) : 0u;
-                }
-                if (flagged) {  // sums are not exact here: decide every valid pixel exactly
-                    dbits = 0;
-                    border = vb;
-                }
-                if (store_lane) dplane[(size_t)out_row * a.strong_pitch + group] = (uint8_t)dbits;
-                n_set += __popc(out_lane ? dbits : 0u);  // one atomic per task, at the end
-                const bool push = out_lane && border != 0;
-                const unsigned ball = __ballot_sync(0xffffffffu, push);
-                if (ball) {
-                    if (push)
-                        gq[qn + __popc(ball & lt_mask)] =
-                          (uint32_t)lane | ((uint32_t)(out_row - r0) << 5) | (border << 14);
-                    qn += __popc(ball);
-                    __syncwarp();
-                    if (qn >= 32) {
-                        const uint32_t st2 = ext_resolve<PixelT>(&a, gq, x0, r0, z,
-                                                                 (uint32_t)qn | ((uint32_t)pqn << 8), 32, false);
-                        qn = st2 & 0xff;
-                        pqn = st2 >> 8;
+                    for (int j = 0; j < 8; ++j)
+                        maybe |= ((vb >> j) & 1u) && (m_hi * Hy[j] > Hx[j] * (Hx[j] + kf));
+                    if (__ballot_sync(0xffffffffu, out_lane && maybe) == 0u) {
+                        hi3 = hi2; hi2 = hi1; hi1 = info;
+                        continue;
                     }
                 }
+                // ---- the row holds a candidate: per-pixel test, store, queue (out of line) -------------
+                const uint2 r2 = ext_row_slow<PixelT>(
+                  &sa, ktab, gq, (uint32_t)qn | ((uint32_t)pqn << 8), make_uint4(Hx[0], Hx[1], Hx[2], Hx[3]),
+                  make_uint4(Hx[4], Hx[5], Hx[6], Hx[7]), make_uint4(Hy[0], Hy[1], Hy[2], Hy[3]),
+                  make_uint4(Hy[4], Hy[5], Hy[6], Hy[7]), vb,
+                  (flagged ? 1u : 0u) | (out_lane ? 2u : 0u) | (store_lane ? 4u : 0u), out_row, group, x0, r0, z);
+                qn = r2.x & 0xff;
+                pqn = r2.x >> 8;
+                n_set += r2.y;  // one atomic per task, at the end
             }
             hi3 = hi2; hi2 = hi1; hi1 = info;
         }
@@ -335,9 +392,9 @@ __global__ void __launch_bounds__(WARPS * 32)
     }
     __syncwarp();
     for (int off = 16; off > 0; off >>= 1) n_set += __shfl_down_sync(0xffffffffu, n_set, off);
-    if (lane == 0 && n_set) atomicAdd(a.strong_count + z, n_set);
+    if (lane == 0 && n_set) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, n_set);
     if (qn > 0 || pqn > 0)
-        ext_resolve<PixelT>(&a, gq, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
+        ext_resolve<PixelT>(&sa, gq, x0, r0, z, (uint32_t)qn | ((uint32_t)pqn << 8), qn, true);
 }
 
 }  // namespace ffsb

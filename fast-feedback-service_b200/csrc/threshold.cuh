@@ -48,7 +48,7 @@ struct ThreshArgs {
     uint32_t* strong_bits;      // output plane(s), pre-zeroed
     size_t strong_pitch;        // bytes per row (multiple of 4)
     size_t strong_frame_stride; // bytes per frame plane
-    unsigned int* strong_count; // per slot, pre-zeroed
+    unsigned int* strong_count; // per slot (slot z at + z * zstride_words), pre-zeroed
     uint32_t* cand;             // per slot: cand_cap entries  col | row << 13
     unsigned int* cand_count;   // per slot, pre-zeroed (may run past cand_cap)
     unsigned int cand_cap;
@@ -72,12 +72,15 @@ struct ThreshArgs {
     uint32_t* bad;          // per slot: bad_cap entries col | row << 13 of mask-valid pixels above tmax,
     unsigned int* bad_count;  // appended by whoever meets one as a centre pixel (may run past bad_cap)
     unsigned int bad_cap;
+    // strong plane, chunk counts and the four counters of a slot live in ONE per-slot region that a
+    // single memset clears (context.cuh d_zero): consecutive slots are zstride_words uint32 apart
+    size_t zstride_words;
 };
 
 // A mask-valid centre pixel above the trusted maximum: remember it for trusted_fixup_kernel.
 __device__ __forceinline__ void note_bad_pixel(const ThreshArgs& a, int z, int col, int row) {
     if (!a.bad_count) return;
-    const unsigned k = atomicAdd(a.bad_count + z, 1u);
+    const unsigned k = atomicAdd(a.bad_count + (size_t)z * a.zstride_words, 1u);
     if (k < a.bad_cap) a.bad[(size_t)z * a.bad_cap + k] = (uint32_t)col | ((uint32_t)row << 13);
 }
 
@@ -424,7 +427,7 @@ __device__ __forceinline__ void set_strong(const ThreshArgs& a, int z, int col, 
     const uint32_t before = atomicOr(w, bit);
     // strong pixels are sparse, so counting them per compaction chunk here (one more atomic
     // per strong pixel) replaces a kernel that re-reads every strong plane (cc_count_kernel)
-    if (a.chunk_count && !(before & bit)) atomicAdd(a.chunk_count + (size_t)z * a.n_chunks + (word >> 10), 1u);
+    if (a.chunk_count && !(before & bit)) atomicAdd(a.chunk_count + (size_t)z * a.zstride_words + (word >> 10), 1u);
 }
 
 // grid: (blocks, n_frames).  One thread per candidate of frame blockIdx.y (grid-stride).
@@ -433,7 +436,7 @@ __global__ void __launch_bounds__(256) resolve_kernel(const ThreshArgs a) {
     const int z = a.slot0 + blockIdx.y;
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
     const uint8_t* valid = a.valid_bits + (size_t)z * a.valid_frame_stride;
-    const unsigned n_cand = a.cand_count[z];
+    const unsigned n_cand = a.cand_count[(size_t)z * a.zstride_words];
     const bool brute = a.force_brute || n_cand > a.cand_cap;
     const long long total = brute ? (long long)a.width * a.height : (long long)n_cand;
     const uint32_t* list = a.cand + (size_t)z * a.cand_cap;
@@ -460,7 +463,7 @@ __global__ void __launch_bounds__(256) resolve_kernel(const ThreshArgs a) {
         }
     }
     for (int off = 16; off > 0; off >>= 1) found += __shfl_down_sync(0xffffffffu, found, off);
-    if ((threadIdx.x & 31) == 0 && found) atomicAdd(a.strong_count + z, found);
+    if ((threadIdx.x & 31) == 0 && found) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, found);
 }
 
 }  // namespace ffsb

@@ -7,7 +7,7 @@ namespace ffsb {
 __device__ __forceinline__ void flush_candidates(const ThreshArgs& a, int z, const uint32_t* q,
                                                  int first, int n, int lane) {
     unsigned base = 0;
-    if (lane == 0) base = atomicAdd(a.cand_count + z, (unsigned)n);
+    if (lane == 0) base = atomicAdd(a.cand_count + (size_t)z * a.zstride_words, (unsigned)n);
     base = __shfl_sync(0xffffffffu, base, 0);
     if (lane < n && base + lane < a.cand_cap)
         a.cand[(size_t)z * a.cand_cap + base + lane] = q[first + lane];

@@ -25,7 +25,7 @@ namespace ffsb {
 template <typename PixelT, int KH>
 __global__ void __launch_bounds__(256) trusted_fixup_kernel(const ThreshArgs a) {
     const int z = a.slot0 + blockIdx.y;
-    const unsigned n_bad = a.bad_count[z];
+    const unsigned n_bad = a.bad_count[(size_t)z * a.zstride_words];
     if (n_bad == 0) return;
     constexpr int KS = 2 * KH + 1;
     const uint8_t* frame = a.image + (size_t)z * a.frame_stride;
@@ -54,24 +54,24 @@ __global__ void __launch_bounds__(256) trusted_fixup_kernel(const ThreshArgs a) 
         const uint32_t bit = 1u << (col & 31);
         if (strong) {
             if (!(atomicOr(w, bit) & bit)) {
-                if (a.chunk_count) atomicAdd(a.chunk_count + (size_t)z * a.n_chunks + (word >> 10), 1u);
+                if (a.chunk_count) atomicAdd(a.chunk_count + (size_t)z * a.zstride_words + (word >> 10), 1u);
                 ++delta;
             }
         } else if (*w & bit) {
             if (atomicAnd(w, ~bit) & bit) {
-                if (a.chunk_count) atomicSub(a.chunk_count + (size_t)z * a.n_chunks + (word >> 10), 1u);
+                if (a.chunk_count) atomicSub(a.chunk_count + (size_t)z * a.zstride_words + (word >> 10), 1u);
                 --delta;
             }
         }
     }
-    if (delta) atomicAdd(a.strong_count + z, (unsigned)delta);
+    if (delta) atomicAdd(a.strong_count + (size_t)z * a.zstride_words, (unsigned)delta);
 }
 
 // grid (blocks, n_frames).  b_bits: the eroded planes (ext2), one per slot.
 template <typename PixelT>
 __global__ void __launch_bounds__(256) trusted_clear_kernel(const ThreshArgs a, uint32_t* b_bits, size_t bits_stride) {
     const int z = a.slot0 + blockIdx.y;
-    const unsigned n_bad = a.bad_count[z];
+    const unsigned n_bad = a.bad_count[(size_t)z * a.zstride_words];
     if (n_bad == 0) return;
     uint32_t* B = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(b_bits) + (size_t)z * bits_stride);
     const int wpr = (int)(a.strong_pitch >> 2);

@@ -1,5 +1,10 @@
+import os
 import sys
 from pathlib import Path
+
+# the library honours its developer knobs (FFS_CAND_CAP, FFS_FORCE_BRUTE, ... used by a few tests to
+# force rare paths) only when this is set; it is read once, at the first call into the library
+os.environ.setdefault("FFS_DEV_KNOBS", "1")
 
 import pytest
 

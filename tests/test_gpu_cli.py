@@ -36,7 +36,7 @@ def write_stream(d: Path, frames, mask, bits, omega_increment=None, start=0):
 
 def run(exe, args, timeout=120, host_decode=False, cwd=None):
     r, w = os.pipe()
-    env = dict(os.environ, FFS_HOST_DECODE="1" if host_decode else "0")
+    env = dict(os.environ, FFS_DEV_KNOBS="1", FFS_HOST_DECODE="1" if host_decode else "0")
     proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=subprocess.PIPE,
                             stderr=subprocess.PIPE, env=env, cwd=cwd)
     os.close(w)

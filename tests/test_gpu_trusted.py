@@ -22,11 +22,11 @@ def overexposed(h, w, dtype, seed, tmax, n_bad=25, lam=2.0):
     ys, xs = rng.integers(0, h, n_bad), rng.integers(0, w, n_bad)
     top = min(np.iinfo(dtype).max, 2 ** 24 + 5) + 1  # exclusive
     img[ys, xs] = rng.integers(tmax + 1, top, n_bad).astype(dtype)
-    img[ys[0], xs[0]] = tmax + 1            # just above: invalid
+    img[ys[0], xs[0]] = tmax + 1            # just above: invalid (tmax < type max in every case here)
     img[ys[1], xs[1]] = tmax                # exactly the cutoff: still valid (v <= max_valid, thresholding.cu:209)
     # a cluster: overlapping neighbourhoods, and a bright spot right next to an invalid pixel
     cy, cx = h // 2, w // 3
-    img[cy:cy + 2, cx:cx + 3] = tmax + 7
+    img[cy:cy + 2, cx:cx + 3] = min(tmax + 7, int(np.iinfo(dtype).max))
     img[cy + 2, cx:cx + 3] = np.minimum(tmax, 900)
     if mask[0, 0]:
         img[0, 0] = tmax + 1                # image corner

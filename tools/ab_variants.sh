@@ -1,4 +1,5 @@
 #!/bin/bash
+export FFS_DEV_KNOBS=1  # the library reads its developer knobs only with this set
 # A/B timing of differently-built copies of the library on ONE box (developer tool):
 #   tools/ab_variants.sh name1 name2 ...   (ffs_b200/variants/libffs_b200_<name>.so; "cur" = the in-tree build)
 V=fast-feedback-service_b200/ffs_b200/variants

@@ -1,4 +1,5 @@
 #!/bin/bash
+export FFS_DEV_KNOBS=1  # the library reads its developer knobs only with this set
 # Developer timing experiments on the fused dispersion kernel (results of modes != 0 are wrong by design):
 #   variants/libffs_b200_dbg.so = make variant NAME=dbg EXTRA="-DFUSED_DEBUG_MODES=1"
 #     FFS_FUSED_DEBUG=5 TMA traffic only; 3 streaming loop + queue pushes; 2 + stage 2 (no exact resolves); 0 everything

@@ -1,6 +1,7 @@
 #!/bin/bash
 # round-2 GPU pass B: full GPU suite, new bench line (all legs), refgpu timing
 set -x
+export FFS_DEV_KNOBS=1
 O=gpurun_out/r2b; mkdir -p $O
 timeout 1700 python -m pytest tests -m gpu -x -q > $O/pytest.log 2>&1; echo "pytest rc=$?" >> $O/pytest.log
 tail -15 $O/pytest.log
