@@ -53,9 +53,11 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
         resolve_kernel<PixelT, 3, true><<<grid, 256, 0, st>>>(a);
     } else {
         // streaming first pass (extended_stream.cuh).  Warps are independent tasks; their number per CTA
-        // only decides how the per-warp shared memory (11 KB) packs into an SM: 10 per CTA -> 2 CTAs =
-        // 20 resident warps (3 per CTA: 18, 4: 16).
-        static const int ext_warps = env_int("FFS_EXT_WARPS", 10);
+        // only decides how the per-warp shared memory (11 KB) packs into an SM: 3 per CTA -> 6 CTAs =
+        // 18 resident warps.  Measured (Eiger2 16M, 32 frames): 3 -> 55.9 us/frame, 4 (16 warps/SM) -> 63.4,
+        // 10 (20 warps/SM) -> 63.1: a CTA's shared memory is released only when its slowest warp ends,
+        // and the kernel is bound by ALU-pipe issue, not by latency, so more resident warps do not pay.
+        static const int ext_warps = env_int("FFS_EXT_WARPS", 3);
         int rc = ext_warps == 3   ? launch_ext_pass1<PixelT, 3>(c, a, n, st)
                  : ext_warps == 4 ? launch_ext_pass1<PixelT, 4>(c, a, n, st)
                                   : launch_ext_pass1<PixelT, 10>(c, a, n, st);
