@@ -108,3 +108,4 @@ static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_stro
 #include "api_sweep.inl"
 #include "api_multi.inl"
 #include "api_shim.inl"
+#include "api_noalloc.inl"

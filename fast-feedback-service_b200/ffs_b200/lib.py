@@ -104,6 +104,8 @@ SYMBOLS = {
     "ffs_sync": (_i, [_vp, _vp]),
     "ffs_get_strong_bits": (_i, [_vp, _i, _vp]),
     "ffs_get_strong_u8": (_i, [_vp, _i, _vp]),
+    "ffs_get_strong_u8_static": (_i, [_vp, _i, _vp]),
+    "ffs_noalloc_max_pixels": (_sz, []),
     "ffs_get_extended_stage_u8": (_i, [_vp, _i, _i, _vp]),
     "ffs_fetch": (_i, [_vp, _i, C.POINTER(FrameResult), _vp, _sz, C.POINTER(_sz)]),
     "ffs_get_labels": (_i, [_vp, _i, _vp]),

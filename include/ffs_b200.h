@@ -167,6 +167,16 @@ int ffs_sync(ffs_ctx *ctx, void *stream);
 /* Parity hooks (synchronous). */
 int ffs_get_strong_bits(ffs_ctx *ctx, int slot, uint8_t *bits_out /* height*ceil(width/8) */);
 int ffs_get_strong_u8(ffs_ctx *ctx, int slot, uint8_t *plane_out /* width*height, 0/1 */);
+/* No counterpart in the reference.  The same result as
+ * ffs_get_strong_u8 for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it): the unpack kernel's scratch is a file-scope device array of
+ * FFS_NOALLOC_MAX_PIXELS bytes (4.5 MiB, held by every GPU that loads the library until exit)
+ * instead of a cudaMalloc'ed buffer, and the call makes no cudaMalloc / cudaFree.  width*height
+ * above the maximum returns FFS_ERR_CAPACITY (ffs_last_error says so).  All calls on one GPU share
+ * the array: calls that overlap on the GPU race (this entry point serialises its own callers). */
+#define FFS_NOALLOC_MAX_PIXELS 4718592 /* 4.5 Mi pixels: Eiger2 4M (2070x2167), Jungfrau 4M (2068x2164) */
+int ffs_get_strong_u8_static(ffs_ctx *ctx, int slot, uint8_t *plane_out /* width*height, 0/1 */);
+size_t ffs_noalloc_max_pixels(void);
 /* Extended algorithm intermediates: stage 1 = first-pass dispersion mask, stage 2 =
  * eroded plane (1 = valid pixel outside the signal core).  width*height bytes. */
 int ffs_get_extended_stage_u8(ffs_ctx *ctx, int slot, int stage, uint8_t *plane_out);
