@@ -609,7 +609,8 @@ def run_gpu_arm(args):
 
     if name == "sweep3600":
         t = sweep_leg(cfg, env, args.sweep_frames)
-        stream_s, synth_s, finish_s, merge_s = reduce_max([t["stream_s"], t["synth_s"], t["finish_s"], t["merge_s"]])
+        stream_s, synth_s, finish_s, merge_s, exch_s = reduce_max([t["stream_s"], t["synth_s"], t["finish_s"],
+                                                                   t["merge_s"], t.get("exchange_s", 0.0)])
         if rank == 0:
             total = stream_s + finish_s + merge_s
             out = {"metric": cfg["metric"], "value": t["frames"] / total, "unit": "frames/s", "n_gpus": world,
@@ -620,7 +621,7 @@ def run_gpu_arm(args):
                    "e2e": {"value": t["frames"] / total, "unit": "frames/s",
                            "h2d_bytes_per_step": t["frames"] * frame_bytes // world, "d2h_bytes_per_step": 0},
                    "sweep": {"stream_s": stream_s, "synth_s_inside_stream": synth_s, "finish_3d_s": finish_s,
-                             "merge_s": merge_s, "components": t["components"],
+                             "merge_s": merge_s, "nccl_exchange_s": exch_s, "components": t["components"],
                              "merge": "native (csrc/api_multi.inl): ncclSend/ncclRecv of boundary planes + "
                                       "ncclAllGather of boundary-component records" if world > 1 else "single slab",
                              "spots_after_filters": t["spots_after_filters"],
