@@ -192,11 +192,11 @@ def run_reference_arm(args):
         return
     cfg = CONFIGS[args.config]
     g = cfg["geom"]
-    n_distinct = 4
+    n_distinct = cfg["distinct"]  # the same frames, and the same frames per step, as the GPU arm's config
     mask, frames = make_inputs(cfg, n_distinct)
     T = cpu_threads(g)
     cpu = CpuPath(mask, T, cfg["algorithm"])
-    per_step = T  # one frame per thread per step: a bounded sample of the stream
+    per_step = args.batch or cfg["batch"]  # a bounded sample of the stream, frame-parallel over T threads
     for _ in range(args.warmup):
         cpu.run(frames, per_step)
     t = sum(cpu.run(frames, per_step) for _ in range(args.steps))

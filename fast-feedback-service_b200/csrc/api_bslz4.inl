@@ -19,7 +19,8 @@ static int bslz4_setup(ffs_ctx* c) {
     FFS_CK(c, cudaSetDevice(c->p.device));
     FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_cap * S, cudaHostAllocDefault));
     FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_cap * S + 64));
-    c->blocks_stride = sizeof(Bslz4Dyn) + sizeof(uint2) * c->max_blocks;
+    // Bslz4Dyn | uint2 {offset, length} per block | uint32 work order (longest payload first)
+    c->blocks_stride = round_up(sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * c->max_blocks, 16);
     FFS_CK(c, cudaHostAlloc(&c->h_blocks, c->blocks_stride * S, cudaHostAllocDefault));
     FFS_CK(c, cudaMalloc(&c->d_blocks, c->blocks_stride * S));
     FFS_CK(c, cudaMalloc(&c->d_dec_status, sizeof(unsigned) * S));
@@ -73,6 +74,18 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
     a.tail_elem0 = (uint32_t)(n - tail);
     a.pad[0] = a.pad[1] = 0;
     *hdr = a;
+    // Work order: longest compressed payload first.  A block's decode time grows with its payload and
+    // the kernel is ~1.15 waves of warps, so the blocks that start last decide when it ends: make those
+    // the cheapest ones (module-gap blocks compress to a few bytes).  Counting sort, O(n_blocks).
+    {
+        uint32_t* order = reinterpret_cast<uint32_t*>(tab + n_blocks);
+        constexpr int kBuckets = 64;
+        uint32_t start[kBuckets + 1] = {};
+        auto bucket = [](uint32_t clen) { return kBuckets - 1 - (int)std::min<uint32_t>(clen >> 7, kBuckets - 1); };
+        for (size_t b = 0; b < n_blocks; ++b) start[bucket(tab[b].y) + 1]++;
+        for (int k = 0; k < kBuckets; ++k) start[k + 1] += start[k];
+        for (size_t b = 0; b < n_blocks; ++b) order[start[bucket(tab[b].y)]++] = (uint32_t)b;
+    }
     return FFS_OK;
 }
 
@@ -167,7 +180,8 @@ extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, si
                               cudaMemcpyHostToDevice, st));
     FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
                               c->h_blocks + (size_t)slot * c->blocks_stride,
-                              sizeof(Bslz4Dyn) + sizeof(uint2) * dyn.n_blocks, cudaMemcpyHostToDevice, st));
+                              sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * dyn.n_blocks,
+                              cudaMemcpyHostToDevice, st));
     s.compressed = true;
     return submit_tail(c, slot, 1, dyn.n_blocks, frame_id, st);
 }
@@ -189,7 +203,8 @@ extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, 
     FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, h, chunk_bytes, cudaMemcpyHostToDevice, st));
     FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
                               c->h_blocks + (size_t)slot * c->blocks_stride,
-                              sizeof(Bslz4Dyn) + sizeof(uint2) * dyn.n_blocks, cudaMemcpyHostToDevice, st));
+                              sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * dyn.n_blocks,
+                              cudaMemcpyHostToDevice, st));
     rc = bslz4_launch(c, slot, dyn.n_blocks, st);
     if (rc) return rc;
     unsigned status = 0;

@@ -41,7 +41,8 @@ static_assert(sizeof(Bslz4Dyn) == 32, "header precedes the uint2 block table");
 
 struct Bslz4Args {
     const uint8_t* chunk;       // device copy of the whole chunk (header + body), 16-byte aligned
-    const Bslz4Dyn* dyn;        // followed by per block: uint2 {payload offset in chunk, payload bytes}
+    const Bslz4Dyn* dyn;        // followed by per block: uint2 {payload offset in chunk, payload bytes},
+                                // then uint32 work order[n_blocks]: warp w decodes block order[w]
     uint8_t* frame;             // pitched destination
     size_t pitch;
     uint32_t width;
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
     const Bslz4Dyn dyn = *a.dyn;
     const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t b = blockIdx.x * WARPS + warp;
+    const uint32_t w_id = blockIdx.x * WARPS + warp;
     constexpr int ES = (int)sizeof(PixelT);
     uint8_t* out = bsmem + (size_t)warp * kBslz4SmemPerWarp;
 
@@ -190,7 +191,12 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
         const uint32_t row = e / a.width, col = e % a.width;
         reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
     }
-    if (b >= dyn.n_blocks) return;
+    if (w_id >= dyn.n_blocks) return;
+    const uint32_t b = reinterpret_cast<const uint32_t*>(blocks + dyn.n_blocks)[w_id];  // longest payload first
+    if (b >= dyn.n_blocks) {
+        if (lane == 0) atomicExch(a.status, 3u);
+        return;
+    }
     const uint2 blk = blocks[b];
     const int n_el = (b + 1 == dyn.n_blocks) ? (int)dyn.last_elems : (int)dyn.block_elems;
     const int out_len = n_el * ES;

@@ -25,6 +25,9 @@
 #pragma once
 #include "dispersion_fused.cuh"
 
+#ifndef EXT_MIN_CTAS
+#define EXT_MIN_CTAS 5  // 3-warp CTAs per SM the first pass is compiled for; 6 (<= 112 registers) spills: 77.9 vs 55.2 us/frame
+#endif
 #ifndef EXT_ROW_UNROLL
 #define EXT_ROW_UNROLL 2  // rows of a stage unrolled together (4 = whole stage: more code, no faster)
 #endif
@@ -120,13 +123,9 @@ __device__ __noinline__ uint32_t ext_resolve(const ThreshArgs* __restrict__ ap, 
 template <typename PixelT>
 __device__ __noinline__ uint2 ext_row_slow(const ThreshArgs* __restrict__ ap, const float4* __restrict__ ktab,
                                            uint32_t* gq, uint32_t state, uint4 hxa, uint4 hxb, uint4 hya, uint4 hyb,
-                                           uint32_t vb, uint32_t flags, int out_row, int group, int x0,
+                                           uint2 mw, uint32_t vb, uint32_t flags, int out_row, int group, int x0,
                                            int r0, int z) {
-    const ThreshArgs& a = *ap;
-    // per-pixel window counts of this group's 8 pixels: a property of the mask (group_info_kernel),
-    // L2-resident across frames; only rows that reach this path read them
-    const uint2 mw = ((flags & 2u) && group < (int)(a.m_pitch >> 3)) ? *reinterpret_cast<const uint2*>(a.mcount + (size_t)out_row * a.m_pitch + 8 * (size_t)group)
-                                  : make_uint2(0u, 0u);
+    const ThreshArgs& a = *ap;  // mw: the per-pixel window counts of this group's 8 pixels (prefetched by the caller)
     const int lane = threadIdx.x & 31;
     const bool flagged = flags & 1u, out_lane = flags & 2u, store_lane = flags & 4u;
     const uint32_t Hx[8] = {hxa.x, hxa.y, hxa.z, hxa.w, hxb.x, hxb.y, hxb.z, hxb.w};
@@ -170,7 +169,7 @@ __device__ __noinline__ uint2 ext_row_slow(const ThreshArgs* __restrict__ ap, co
 }
 
 template <typename PixelT, int STAGES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
   ext_pass1_kernel(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_info4,
                    const __grid_constant__ ThreshArgs a) {
     using G = FusedGeo<PixelT>;
@@ -254,6 +253,13 @@ __global__ void __launch_bounds__(WARPS * 32)
     uint32_t Vy[8] = {0, 0, 0, 0, 0, 0, 0, 0};     // column sums of the squares
     uint32_t big7 = 0;                             // bit r: row i-r of this lane holds a pixel > CLAMP
     uint32_t hi1 = 0, hi2 = 0, hi3 = 0;            // group info of rows i-1, i-2, i-3
+    // per-pixel window counts (one byte each) of this lane's group in rows i-1, i-2, i-3.  A group whose
+    // valid pixels all have a full window (info bit 14) is 49 everywhere; the others -- next to a module
+    // gap, the image edge or a dead pixel -- read theirs from the mask's count plane (L2-resident) when
+    // the row is LOADED, three row iterations before it is the centre row: the latency never shows.
+    constexpr uint32_t kFull4 = 0x31313131u;  // 49, 49, 49, 49
+    uint2 mq1 = make_uint2(kFull4, kFull4), mq2 = mq1, mq3 = mq1;
+    const uint32_t kf49 = ktabi[49];
     uint8_t* ring_lane = ring + lane * 16;
     const int pimg_off = lane * PPL * (int)sizeof(PixelT);
     const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 4 * lane;
@@ -270,6 +276,9 @@ __global__ void __launch_bounds__(WARPS * 32)
             const int i = g * SR + u;
             // ---- load, mask, clamp ------------------------------------------------------------
             const uint32_t info = *reinterpret_cast<const uint32_t*>(st + pinfo_off + u * E::INFO4_ROW_BYTES);
+            uint2 mq0 = make_uint2(kFull4, kFull4);
+            if ((info & 0xffu) && !(info & 0x4000u))  // (rows / groups outside the image are zero-filled: info == 0)
+                mq0 = *reinterpret_cast<const uint2*>(a.mcount + (size_t)(y_first + i) * a.m_pitch + 8 * (size_t)group);
             uint32_t c[4];
             bool big;
             if constexpr (sizeof(PixelT) == 2) {
@@ -352,22 +361,31 @@ __global__ void __launch_bounds__(WARPS * 32)
                 Hy[0] = Ey[0] + Ey[1] + Ey[2] + Ey[3] + Ey[4] + Ey[5] + Ey[6];
 #pragma unroll
                 for (int j = 1; j < 8; ++j) Hy[j] = Hy[j - 1] + Ey[j + 6] - Ey[j - 1];
-                // ---- row prune: on background the test fails by a wide margin for every pixel.  With
-                // m_hi >= m >= m_lo over the group's valid pixels (both in the 4-byte group info) and K increasing in m,
-                //     m_hi * y <= x * (x + floor(K(m_lo) g_lo))   ==>   m*y - x^2 <= x K(m) g   ==>   D = 0
-                // in exact 32-bit integers (m*y < 49 * 2^26, x (x + K) < 3.3e9).  Only when some lane of
-                // the warp has a pixel that survives does the row take the per-pixel fp32 path below;
-                // the D plane is pre-zeroed, so a pruned row stores nothing.
+                // ---- row prune: on background the test fails by a wide margin for every pixel:
+                //     m * y <= x * (x + floor(K(m) g_lo))   ==>   m*y - x^2 <= x K(m) g   ==>   D = 0
+                // in exact 32-bit integers (m*y < 49 * 2^26, x (x + K) < 3.3e9) with the pixel's own m.
+                // Only when some lane of the warp has a pixel that survives (5 % of the rows on the
+                // synthetic frames) does the row take the per-pixel fp32 path; the D plane is pre-zeroed,
+                // so a pruned row stores nothing.  (A bound with one m per group, m_hi * y <= x (x + K(m_lo)),
+                // left 65 % of the rows unpruned: every strip that holds a module-gap or image edge.)
                 const uint32_t vb = hi3 & 0xffu;  // validity of the centre row's pixels
                 {
-                    const uint32_t m_hi = (hi3 >> 8) & 0x3fu, m_lo = (hi3 >> 16) & 0x3fu;
-                    const uint32_t kf = ktabi[m_lo];
                     bool maybe = flagged;
+                    if (mq3.x == kFull4 && mq3.y == kFull4) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        maybe |= ((vb >> j) & 1u) && (m_hi * Hy[j] > Hx[j] * (Hx[j] + kf));
+                        for (int j = 0; j < 8; ++j)  // (without the validity test gap pixels send rows to the
+                            // slow path: 55.3 vs 52.5 us per frame, u32 78.5 vs 69.7, same box)
+                            maybe |= ((vb >> j) & 1u) && (49u * Hy[j] > Hx[j] * (Hx[j] + kf49));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const uint32_t mj = ((j < 4 ? mq3.x : mq3.y) >> (8 * (j & 3))) & 0x3fu;
+                            maybe |= ((vb >> j) & 1u) && (mj * Hy[j] > Hx[j] * (Hx[j] + ktabi[mj]));
+                        }
+                    }
                     if (__ballot_sync(0xffffffffu, out_lane && maybe) == 0u) {
                         hi3 = hi2; hi2 = hi1; hi1 = info;
+                        mq3 = mq2; mq2 = mq1; mq1 = mq0;
                         continue;
                     }
                 }
@@ -375,13 +393,14 @@ __global__ void __launch_bounds__(WARPS * 32)
                 const uint2 r2 = ext_row_slow<PixelT>(
                   &sa, ktab, gq, (uint32_t)qn | ((uint32_t)pqn << 8), make_uint4(Hx[0], Hx[1], Hx[2], Hx[3]),
                   make_uint4(Hx[4], Hx[5], Hx[6], Hx[7]), make_uint4(Hy[0], Hy[1], Hy[2], Hy[3]),
-                  make_uint4(Hy[4], Hy[5], Hy[6], Hy[7]), vb,
+                  make_uint4(Hy[4], Hy[5], Hy[6], Hy[7]), mq3, vb,
                   (flagged ? 1u : 0u) | (out_lane ? 2u : 0u) | (store_lane ? 4u : 0u), out_row, group, x0, r0, z);
                 qn = r2.x & 0xff;
                 pqn = r2.x >> 8;
                 n_set += r2.y;  // one atomic per task, at the end
             }
             hi3 = hi2; hi2 = hi1; hi1 = info;
+            mq3 = mq2; mq2 = mq1; mq1 = mq0;
         }
         __syncwarp();  // see dispersion_fused.cuh on this read-then-async-write reuse
         if (g + STAGES < n_groups && ptx::elect_one()) issue(g + STAGES, s);

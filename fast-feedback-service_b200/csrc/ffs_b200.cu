@@ -75,7 +75,7 @@ static inline cudaStream_t pick_stream(ffs_ctx* c, void* s) {
 }
 
 // Developer A/B knobs (FFS_TWO_KERNEL, FFS_FORCE_BRUTE, FFS_TILE_ROWS, ... -- the table is in
-// DESIGN.md section 8) are read ONLY when FFS_DEV_KNOBS=1 is set as well, so a stray variable in a
+// DESIGN.md section 9) are read ONLY when FFS_DEV_KNOBS=1 is set as well, so a stray variable in a
 // service environment cannot silently change (or slow down 20x) the product path.
 static int env_int(const char* name, int dflt) {
     static const bool dev = [] {
