@@ -9,6 +9,7 @@ import pytest
 from bslz4_ref import compress_chunk as py_compress
 from ffs_b200 import bslz4_encode, lib, synth
 from ffs_b200.spotfinder import FfsError, Spotfinder
+from oracle import oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -118,3 +119,21 @@ def test_full_size_frame_roundtrip():
     assert len(chunk) < f.nbytes / 3
     with Spotfinder(g.width, g.height, np.uint16, mask, n_slots=1) as sf:
         assert np.array_equal(sf.decode_chunk(chunk), f)
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+def test_header_block_size_zero_means_the_default(dtype):
+    """The reference calls bshuf_decompress_lz4(buffer + 12, out, n, elem_size, block_size = 0)
+    (spotfinder/spotfinder.cc:830-834): it never reads the header's block-size field, it lets
+    bitshuffle pick its default (8192 bytes per block).  A chunk whose header says 0 must decode
+    like one that names the default."""
+    g = synth.small_geometry(500, 300)
+    mask = synth.make_mask(g)
+    f = synth.make_frame(g, mask, dtype, config=2, frame_index=5, n_spots=20)
+    chunk = bytearray(bslz4_encode.compress_chunk(f))
+    assert int.from_bytes(chunk[8:12], "big") == 8192
+    chunk[8:12] = (0).to_bytes(4, "big")
+    assert np.array_equal(host_decode(bytes(chunk), f.size, dtype).reshape(f.shape), f)
+    assert np.array_equal(oracle.bslz4_decode(bytes(chunk), dtype, f.size).reshape(f.shape), f)
+    with Spotfinder(g.width, g.height, dtype, mask, n_slots=1) as sf:
+        assert np.array_equal(sf.decode_chunk(bytes(chunk)), f)
