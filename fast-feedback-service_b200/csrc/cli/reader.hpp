@@ -2,8 +2,8 @@
 // (h5read/include/h5read.h:173-204) and the /dev/shm Eiger-stream reader
 // (spotfinder/shmread.cc:13-93): JSON header `start_1`, int32 pixel mask `start_5`
 // (valid = !value), one bitshuffle-LZ4 chunk per frame in `image_%06d_2`; the directory is
-// ready once `start_1` and `start_4` exist.  HDF5 and CBF inputs need libraries that are not
-// available here (see DESIGN.md "Out of scope").
+// ready once `start_1` and `start_4` exist.  NeXus / HDF5 input is reader_h5.hpp (on the
+// in-tree h5lite.hpp, no libhdf5); CBF input is out of scope.
 #pragma once
 #include <array>
 #include <fcntl.h>
@@ -30,6 +30,10 @@ class Reader {
     // Returns the chunk size, 0 when the file is not (completely) there yet, or SIZE_MAX when
     // it does not fit `capacity` (nothing useful is in dst then).
     virtual size_t read_raw_chunk(size_t index, uint8_t* dst, size_t capacity) = 0;
+    // Sources whose frames are stored without a compression filter hand out pixels instead of
+    // chunks: read_pixels copies frame `index` (bytes = slow * fast * element size) into dst.
+    virtual bool chunks_are_raw_pixels() const { return false; }
+    virtual bool read_pixels(size_t /*index*/, void* /*dst*/, size_t /*bytes*/) { return false; }
     virtual size_t get_number_of_images() const = 0;
     virtual std::array<size_t, 2> image_shape() const = 0;  // {slow, fast}
     virtual size_t get_element_size() const = 0;

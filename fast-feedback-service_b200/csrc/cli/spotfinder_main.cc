@@ -16,6 +16,8 @@
 #include "bslz4.hpp"
 #include "png_writer.hpp"
 #include "reader.hpp"
+#include "reader_h5.hpp"
+#include "h5_results.hpp"
 
 #ifndef FFS_VERSION
 #define FFS_VERSION "b200-0.1.0"
@@ -130,8 +132,13 @@ int main(int argc, char** argv) {
         printf("Error: CBF input is not supported by this build\n");
         return 1;
     } else {
-        printf("Error: HDF5 input is not supported by this build (libhdf5 unavailable); pass a stream directory\n");
-        return 1;
+        wait_for_ready(file, H5Read::is_ready_for_read, args.timeout);
+        try {
+            reader_ptr = std::make_unique<H5Read>(file);
+        } catch (const std::exception& e) {
+            printf("%s\n", e.what());
+            return 1;
+        }
     }
     Reader& reader = *reader_ptr;
     const size_t bytes_per_pixel = reader.get_element_size();

@@ -68,7 +68,8 @@
     if (timing_report)
         for (ffs_ctx* c : ctxs) ffs_frame_timing(c, 1);
     if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain; use tests/validate_stream.py\n");
-    if (args.save_h5) printf("Note: results_ffs.h5 cannot be written by this build (libhdf5 unavailable)\n");
+    // --save-h5 on stills: kept centroids per image, keyed by image number (spotfinder.cc:706-721,928-932)
+    std::map<int, std::vector<float>> reflection_centers_2d;
     std::unique_ptr<PipeHandler> pipe;
     if (args.pipe_fd != -1) pipe = std::make_unique<PipeHandler>(args.pipe_fd);
     // Rotation data: every GPU owns a CONTIGUOUS slab of frames (3D components couple consecutive
@@ -133,6 +134,25 @@
             // and decoded on the device (bslz4_gpu.cuh).  The reference decompresses here on the
             // host (spotfinder.cc:823-841); that path is kept for chunks the device decoder does
             // not take (FFS_HOST_DECODE=1 forces it).
+            if (reader.chunks_are_raw_pixels()) {
+                // a source stored without a compression filter (reader_h5.hpp): pixels go straight
+                // into the pinned ring slot
+                if (!reader.read_pixels(offset_image_num, pinned, px * sizeof(pixel_t))) {
+                    printf("Error: could not read image %zu\n", offset_image_num);
+                    g_stop = true;
+                    had_error = true;
+                    ffs_release(ctx, slot);
+                    break;
+                }
+                if (ffs_submit(ctx, slot, image_num) != FFS_OK) {
+                    printf("Error: submit failed: %s\n", ffs_last_error(ctx));
+                    g_stop = true;
+                    had_error = true;
+                    break;
+                }
+                submitted[dev]++;
+                continue;
+            }
             void* pchunk = nullptr;
             size_t cap = 0;
             const bool direct = !host_decode && ffs_slot_buffers(ctx, slot, nullptr, &pchunk, &cap) == FFS_OK;
@@ -231,6 +251,11 @@
                     if (i) centers += ",";
                     centers += jsonmini::number(spots[i].com_x) + "," + jsonmini::number(spots[i].com_y) + "," +
                                jsonmini::number(spots[i].com_z);
+                }
+                if (args.save_h5) {  // print_mutex is held
+                    auto& v = reflection_centers_2d[(int)(image_num + args.start_index)];
+                    v.clear();
+                    for (size_t i = 0; i < kept; ++i) v.insert(v.end(), {spots[i].com_x, spots[i].com_y, spots[i].com_z});
                 }
             }
             if (pipe) {  // keys in sorted order, as nlohmann::json dumps them (spotfinder.cc:997-1008)
@@ -397,12 +422,17 @@
         if (rs > 0) printf("Filtered %zu spots with size < %u pixels\n", rs, args.min_spot_size_3d);
         if (rp > 0) printf("Filtered %zu spots with peak-centroid distance > %s\n", rp, shortest(args.max_peak_centroid_separation).c_str());
         printf("Found %zu spots\n", kept);
+        std::vector<double> kept_var_b, kept_var_m;
+        std::vector<int> kept_depth;
         {   // estimated global values over the kept reflections (spotfinder.cc:1180-1212)
             double sum_b = 0, sum_m = 0;
             size_t n_m = 0, j = 0;
             for (size_t i = 0; i < kept; ++i) {
                 while (j < n3 && labels3[j] != s3[i].label) ++j;  // the filter is stable
                 if (j == n3) break;
+                kept_var_b.push_back(var_b[j]);
+                kept_var_m.push_back(var_m[j]);
+                kept_depth.push_back(depth[j]);
                 sum_b += var_b[j];
                 if (depth[j] >= 5) {  // min_bbox_depth
                     sum_m += var_m[j];
@@ -420,7 +450,47 @@
                     << "] Z: [" << s3[i].z_min << ", " << s3[i].z_max << "] COM: (" << s3[i].com_x << ", " << s3[i].com_y
                     << ", " << s3[i].com_z << ")\n";
         }
+        if (args.save_h5) {  // spotfinder.cc:1219-1257
+            try {
+                std::vector<double> flat_coms;
+                flat_coms.reserve(kept * 3);
+                for (size_t i = 0; i < kept; ++i) flat_coms.insert(flat_coms.end(), {s3[i].com_x, s3[i].com_y, s3[i].com_z});
+                h5results::Table table;
+                table.add_column("xyzobs.px.value", kept, 3, flat_coms);
+                std::vector<int> id(kept, (int)table.get_experiment_ids()[0]);
+                table.add_column("id", kept, 1, id);
+                table.add_column("sigma_b_variance", kept_var_b.size(), 1, kept_var_b);
+                table.add_column("sigma_m_variance", kept_var_m.size(), 1, kept_var_m);
+                table.add_column("spot_extent_z", kept_depth.size(), 1, kept_depth);
+                table.write("results_ffs.h5", "dials/processing/group_0");
+                printf("Successfully wrote 3D reflections to HDF5 file\n");
+            } catch (const std::exception& e) {
+                printf("Error writing data to HDF5 file: %s\n", e.what());
+            }
+        }
         ffs_free(s3);
+        printf("3D spot analysis complete\n");
+    } else if (args.save_h5) {  // stills: spotfinder.cc:1258-1299
+        printf("Processing 2D spots\n");
+        try {
+            std::vector<double> flat_coms;
+            std::vector<int> ids;
+            int id = 0;
+            for (const auto& kv : reflection_centers_2d) {  // std::map: ascending image number
+                for (float c : kv.second) flat_coms.push_back((double)c);
+                ids.insert(ids.end(), kv.second.size() / 3, id);
+                ++id;
+            }
+            h5results::Table table;  // one experiment per image
+            for (int i = 0; i < id - 1; ++i) table.generate_new_attributes();
+            table.add_column("xyzobs.px.value", flat_coms.size() / 3, 3, flat_coms);
+            table.add_column("id", ids.size(), 1, ids);
+            table.write("results_ffs.h5", "dials/processing/group_0");
+            printf("Successfully wrote %zu 2D reflections to HDF5 file\n", ids.size());
+        } catch (const std::exception& e) {
+            printf("Error writing data to HDF5 file: %s\n", e.what());
+        }
+        printf("2D spot analysis complete\n");
     }
 
     const double total_time = seconds_since(all_images_start);

@@ -1,0 +1,171 @@
+"""The executables on NeXus / HDF5 input and with --save-h5:
+`spotfinder FILE.nxs` as the reference's tests drive it (tests/test_spotfinder.py:40-76 of the
+reference) and the results_ffs.h5 table the reference's tests read back (:78-114).  Files are
+produced by h5lite_tool stream2nxs (VDS master + bitshuffle-LZ4 data files) and read back with
+the independent Python parser (tests/h5dissect.py)."""
+import json
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import h5dissect
+from ffs_b200 import synth
+from oracle import oracle
+from test_gpu_cli import BIN, run, write_stream
+
+pytestmark = pytest.mark.gpu
+TOOL = BIN / "h5lite_tool"
+DET = json.dumps({"pixel_size_x": 0.075, "pixel_size_y": 0.075, "beam_center_x": 11.0, "beam_center_y": 7.5,
+                  "distance": 150.0, "image_size_x": 300, "detector": "Eiger"})
+
+
+def to_nxs(stream_dir, prefix, per_file=0):
+    subprocess.run([str(TOOL), "stream2nxs", str(stream_dir), str(prefix), str(per_file)], check=True,
+                   capture_output=True, timeout=120)
+    return str(prefix) + ".nxs"
+
+
+def expected_stills(frames, mask):
+    out = []
+    for f in frames:
+        strong = oracle.dispersion(f, mask)
+        _, spots = oracle.connected_components(strong, f, want_labels=False)
+        kept, _, _ = oracle.filter_spots(spots, 3, 2.0)
+        out.append((int(strong.sum()), int((spots["num_pixels"] >= 3).sum()), kept))
+    return out
+
+
+@pytest.mark.parametrize("exe,dtype,bits", [("spotfinder", np.uint16, 16), ("spotfinder32", np.uint32, 32)])
+def test_nxs_input_same_results_as_the_stream(tmp_path, exe, dtype, bits):
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 7, dtype, config=8, n_spots=12)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, bits)
+    nxs = to_nxs(sd, tmp_path / "scan", per_file=3)  # three data files behind one VDS
+    rc, lines, out, err = run(exe, [nxs, "--threads", "3", "--output-for-index"])
+    assert rc == 0, out + err
+    assert "Total data size: 7x200x300" in out and "Mask has 60000 elements" in out
+    assert sorted(l["file-number"] for l in lines) == list(range(7))
+    want = expected_stills(frames, mask)
+    for l in lines:
+        strong, n_spots, kept = want[l["file-number"]]
+        assert l["file"] == nxs
+        assert l["num_strong_pixels"] == strong and l["n_spots_total"] == n_spots
+        coms = np.stack([kept["com_x"], kept["com_y"], kept["com_z"]], axis=1).astype(np.float64).ravel()
+        assert np.allclose(l["spot_centers"], coms, rtol=1e-5, atol=1e-4)
+    # geometry and wavelength come from the NXmx metadata when --detector / --wavelength are absent
+    assert "Got wavelength from file: 0.976" in out
+    assert re.search(r"Distance:\s+150\.0 mm", out)
+    # the same frames through the stream directory give the same lines
+    rc2, lines2, _, _ = run(exe, [str(sd), "--threads", "3", "--output-for-index"])
+    assert rc2 == 0
+    strip = lambda ls: sorted((l["file-number"], l["n_spots_total"], l["num_strong_pixels"], tuple(l["spot_centers"])) for l in ls)
+    assert strip(lines) == strip(lines2)
+
+
+def test_nxs_wrong_bit_depth_exit_code(tmp_path):
+    g = synth.small_geometry(96, 64)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 2, np.uint32, config=8, n_spots=3)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 32)
+    nxs = to_nxs(sd, tmp_path / "scan")
+    rc, _, out, _ = run("spotfinder", [nxs])
+    assert rc == 32 and "Data type mismatch" in out   # the service re-runs with spotfinder32 (service.py:480-492)
+
+
+def test_not_an_hdf5_file_is_an_error(tmp_path):
+    p = tmp_path / "junk.nxs"
+    p.write_bytes(b"this is not HDF5" * 100)
+    rc, _, out, _ = run("spotfinder", [str(p), "--timeout", "0.3"])
+    assert rc == 1 and "Waited too long" in out
+
+
+def test_uncompressed_dataset_is_read_as_pixels(tmp_path):
+    """Data files written without a compression filter (`stream2nxs ... raw`): the frame loop takes
+    pixels instead of chunks (Reader::chunks_are_raw_pixels / read_pixels)."""
+    g = synth.small_geometry(96, 64)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 3, np.uint16, config=8, n_spots=4)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 16)
+    r = subprocess.run([str(TOOL), "stream2nxs", str(sd), str(tmp_path / "raw"), "0", "raw"], capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr.decode()
+    f = h5dissect.File(tmp_path / "raw_000001.h5")
+    assert f.get("/data").filters() == []
+    rc, lines, out, err = run("spotfinder", [str(tmp_path / "raw.nxs"), "--threads", "2"])
+    assert rc == 0, out + err
+    want = expected_stills(frames, mask)
+    assert sorted((l["file-number"], l["num_strong_pixels"], l["n_spots_total"]) for l in lines) == [
+        (i, want[i][0], want[i][1]) for i in range(3)]
+
+
+def test_save_h5_stills(tmp_path):
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 5, np.uint16, config=8, n_spots=12)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 16)
+    outdir = tmp_path / "out"
+    outdir.mkdir()
+    rc, lines, out, err = run("spotfinder", [str(sd), "--threads", "2", "--save-h5", "--detector", DET], cwd=outdir)
+    assert rc == 0 and err == ""
+    want = expected_stills(frames, mask)
+    n = sum(len(k) for _, _, k in want)
+    assert f"Successfully wrote {n} 2D reflections to HDF5 file" in out and "2D spot analysis complete" in out
+    f = h5dissect.File(outdir / "results_ffs.h5")
+    grp = f.get("/dials/processing/group_0")
+    a = grp.attrs()
+    assert a["experiment_ids"].tolist() == list(range(5)) and len(set(a["identifiers"])) == 5   # one per image
+    assert sorted(grp.links()) == ["id", "xyzobs.px.value"]
+    xyz = f.get("/dials/processing/group_0/xyzobs.px.value").read()
+    ids = f.get("/dials/processing/group_0/id").read()
+    assert xyz.dtype == np.float64 and xyz.shape == (n, 3) and ids.dtype == np.int32 and ids.shape == (n,)
+    exp_ids = np.concatenate([np.full(len(k), i) for i, (_, _, k) in enumerate(want)])
+    assert np.array_equal(ids, exp_ids)
+    exp_xyz = np.concatenate([np.stack([k["com_x"], k["com_y"], k["com_z"]], axis=1) for _, _, k in want]).astype(np.float64)
+    assert np.allclose(xyz, exp_xyz, rtol=1e-5, atol=1e-4)
+    # the reference's own check of this file (tests/test_spotfinder.py:98-106): x within the image
+    assert xyz[:, 0].min() >= 0 and xyz[:, 0].max() <= 300 and (xyz[:, 2] == 0).all()
+
+
+def test_save_h5_rotation_from_nxs(tmp_path):
+    g = synth.small_geometry(240, 180)
+    mask = synth.make_mask(g)
+    sweep = synth.make_sweep(g, mask, 8, np.uint16, n_reflections=40)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, sweep, mask, 16, omega_increment=0.1)
+    nxs = to_nxs(sd, tmp_path / "sweep", per_file=5)
+    outdir = tmp_path / "out"
+    outdir.mkdir()
+    rc, lines, out, err = run("spotfinder", [nxs, "--threads", "2", "--save-h5"], cwd=outdir)
+    assert rc == 0, out + err
+    assert "Oscillation:" in out and "Successfully wrote 3D reflections to HDF5 file" in out
+    strong = np.stack([oracle.dispersion(f, mask) for f in sweep])
+    labels, spots = oracle.connected_components(strong, sweep)
+    kept, _, _ = oracle.filter_spots(spots, 3, 2.0)
+    h, w = mask.shape
+    geom = dict(distance_mm=150.0, beam_center_x_px=w / 2, beam_center_y_px=h / 2, pixel_size_x_mm=0.075,
+                pixel_size_y_mm=0.075, wavelength=0.976, oscillation_width_deg=0.1)
+    sb, sm, depth = oracle.kabsch_variances(labels, sweep, kept, geom)
+    f = h5dissect.File(outdir / "results_ffs.h5")
+    grp = f.get("/dials/processing/group_0")
+    assert sorted(grp.links()) == ["id", "sigma_b_variance", "sigma_m_variance", "spot_extent_z", "xyzobs.px.value"]
+    assert grp.attrs()["experiment_ids"].tolist() == [0]
+    col = lambda name: f.get(f"/dials/processing/group_0/{name}").read()
+    xyz = col("xyzobs.px.value")
+    assert xyz.shape == (len(kept), 3)
+    exp = np.stack([kept["com_x"], kept["com_y"], kept["com_z"]], axis=1).astype(np.float64)
+    assert np.allclose(xyz, exp, rtol=1e-5, atol=1e-4)
+    assert (col("id") == 0).all() and col("id").dtype == np.int32
+    assert np.array_equal(col("spot_extent_z"), depth)
+    assert np.allclose(col("sigma_b_variance"), sb, rtol=1e-4, atol=1e-12)
+    assert np.allclose(col("sigma_m_variance"), sm, rtol=1e-4, atol=1e-12)
