@@ -133,7 +133,7 @@ def test_save_h5_stills(tmp_path):
     exp_xyz = np.concatenate([np.stack([k["com_x"], k["com_y"], k["com_z"]], axis=1) for _, _, k in want]).astype(np.float64)
     assert np.allclose(xyz, exp_xyz, rtol=1e-5, atol=1e-4)
     # the reference's own check of this file (tests/test_spotfinder.py:98-106): x within the image
-    assert xyz[:, 0].min() >= 0 and xyz[:, 0].max() <= 300 and (xyz[:, 2] == 0).all()
+    assert xyz[:, 0].min() >= 0 and xyz[:, 0].max() <= 300 and (xyz[:, 2] == 0.5).all()  # one plane: z + 0.5
 
 
 def test_save_h5_rotation_from_nxs(tmp_path):
