@@ -1340,10 +1340,11 @@ class Writer {
         std::vector<uint8_t> bytes;
     };
     struct Node {
-        enum Kind { Group, Dataset, SoftLink } kind = Group;
+        enum Kind { Group, Dataset, SoftLink, ExternalLink } kind = Group;
         std::map<std::string, std::unique_ptr<Node>> children;  // Group
         std::vector<AttrSpec> attrs;
-        std::string soft_target;
+        std::string soft_target;                 // SoftLink: path; ExternalLink: object path in the other file
+        std::string external_file;               // ExternalLink
         // Dataset
         Datatype dtype;
         std::vector<uint64_t> dims, maxdims, chunk;
@@ -1602,7 +1603,63 @@ class Writer {
         write_header(n.addr, msgs);
     }
 
+    // A group that holds an external link cannot be a symbol table (its entries know hard and soft
+    // links only): it is written the way libhdf5 writes "compact" new-style groups -- a link info
+    // message, a group info message and one link message per child in the object header.
+    void emit_compact_group(Node& g) {
+        if (g.children.size() > 8) throw Error("h5lite: a group with external links holds at most 8 links (compact storage)");
+        std::vector<Msg> msgs;
+        std::vector<uint8_t> linfo(18, 0xff);
+        linfo[0] = 0, linfo[1] = 0;
+        msgs.push_back({0x02, 0, linfo});
+        msgs.push_back({0x0A, 1, {0, 0}});
+        const size_t first_link = msgs.size();
+        auto link_msg = [&](const std::string& name, const Node& c) {
+            if (name.size() > 255) throw Error("h5lite: link name too long");
+            std::vector<uint8_t> m;
+            m.push_back(1);
+            m.push_back(c.kind == Node::Group || c.kind == Node::Dataset ? 0 : 8);
+            if (c.kind == Node::SoftLink) m.push_back(1);
+            if (c.kind == Node::ExternalLink) m.push_back(64);
+            m.push_back((uint8_t)name.size());
+            m.insert(m.end(), name.begin(), name.end());
+            if (c.kind == Node::Group || c.kind == Node::Dataset) {
+                m.resize(m.size() + 8);
+                wr_le(&m[m.size() - 8], c.addr, 8);
+            } else if (c.kind == Node::SoftLink) {
+                m.resize(m.size() + 2);
+                wr_le(&m[m.size() - 2], c.soft_target.size(), 2);
+                m.insert(m.end(), c.soft_target.begin(), c.soft_target.end());
+            } else {
+                const size_t vlen = 1 + c.external_file.size() + 1 + c.soft_target.size() + 1;
+                m.resize(m.size() + 2);
+                wr_le(&m[m.size() - 2], vlen, 2);
+                m.push_back(0);  // version 0, flags 0
+                m.insert(m.end(), c.external_file.begin(), c.external_file.end());
+                m.push_back(0);
+                m.insert(m.end(), c.soft_target.begin(), c.soft_target.end());
+                m.push_back(0);
+            }
+            return m;
+        };
+        for (const auto& kv : g.children) msgs.push_back({0x06, 0, link_msg(kv.first, *kv.second)});
+        const size_t first_attr = msgs.size();
+        for (const auto& a : g.attrs) msgs.push_back({0x0C, 0, attr_msg(a, false)});
+        g.addr = alloc(header_size(msgs));
+        g.btree = g.heap = UNDEF;
+        size_t i = first_link;
+        for (auto& kv : g.children) {
+            if (kv.second->kind == Node::Group) emit_group(*kv.second);
+            else if (kv.second->kind == Node::Dataset) emit_dataset(*kv.second);
+            msgs[i++].body = link_msg(kv.first, *kv.second);
+        }
+        for (size_t k = 0; k < g.attrs.size(); ++k) msgs[first_attr + k].body = attr_msg(g.attrs[k], true);
+        write_header(g.addr, msgs);
+    }
+
     void emit_group(Node& g) {
+        for (const auto& kv : g.children)
+            if (kv.second->kind == Node::ExternalLink) return emit_compact_group(g);
         std::vector<Msg> msgs;
         msgs.push_back({0x11, 0, std::vector<uint8_t>(16, 0)});
         for (const auto& a : g.attrs) msgs.push_back({0x0C, 0, attr_msg(a, false)});
@@ -1667,7 +1724,8 @@ class Writer {
                     put(e + 8, UNDEF, 8), put(e + 16, 2, 4), put(e + 24, target_off[it->first], 4);
                 } else {
                     put(e + 8, c.addr, 8);
-                    if (c.kind == Node::Group) put(e + 16, 1, 4), put(e + 24, c.btree, 8), put(e + 32, c.heap, 8);
+                    if (c.kind == Node::Group && c.btree != UNDEF)  // a compact group has no B-tree / heap to cache
+                        put(e + 16, 1, 4), put(e + 24, c.btree, 8), put(e + 32, c.heap, 8);
                 }
                 last = it->first;
             }
@@ -1787,6 +1845,14 @@ class Writer {
         if (slot) throw Error("h5lite: " + name + " already exists");
         slot = std::make_unique<Node>();
         slot->kind = Node::SoftLink, slot->soft_target = target;
+    }
+
+    // Link to `path` inside another file; `file` is taken relative to the directory of this one.
+    static void external_link(Node* g, const std::string& name, const std::string& file, const std::string& path) {
+        auto& slot = g->children[name];
+        if (slot) throw Error("h5lite: " + name + " already exists");
+        slot = std::make_unique<Node>();
+        slot->kind = Node::ExternalLink, slot->external_file = file, slot->soft_target = path;
     }
 
     static void attr_raw(Node* n, const std::string& name, const Datatype& dt, const std::vector<uint64_t>& dims,

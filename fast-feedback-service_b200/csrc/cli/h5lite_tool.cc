@@ -13,12 +13,13 @@
 //                                         (two B-tree levels), a 300-chunk dataset, ragged edge chunks,
 //                                         soft links, fixed-length string and numeric attributes
 //   h5lite_tool selection HEX             decode one serialised dataspace selection
-//   h5lite_tool stream2nxs DIR PREFIX [FRAMES_PER_FILE [raw|links]]
+//   h5lite_tool stream2nxs DIR PREFIX [FRAMES_PER_FILE [raw|links|external]]
 //                                         an Eiger stream directory (start_1, start_5, image_*_2) as
 //                                         PREFIX.nxs (NXmx metadata + VDS) and PREFIX_NNNNNN.h5 data
 //                                         files (one bitshuffle-LZ4 chunk per frame, filter 32008;
 //                                         `raw`: decoded pixels, no filter; `links`: no VDS, frames
-//                                         in the master as /entry/data/data_NNNNNN)
+//                                         in the master as /entry/data/data_NNNNNN; `external`:
+//                                         VDS sources reached through external links in the master)
 //
 // tests/test_h5lite.py drives it; `stream2nxs` is also how a recorded stream is turned into the
 // file layout the reference's H5Read opens (h5read.c:1088-1127).
@@ -236,6 +237,9 @@ static int cmd_stream2nxs(const std::string& dir, const std::string& prefix, siz
     // "links": no VDS and no separate files -- the frames sit in the master as /entry/data/data_000001,
     // data_000002, ... (the group layout of the Eiger file writer)
     const bool links = mode == "links";
+    // "external": the master reaches the data files through external links /entry/data/data_NNNNNN,
+    // and the VDS names them as sources in file "." -- the case h5read.c:945-985 dereferences
+    const bool external = mode == "external";
     Writer master;
     const auto hdr = slurp(dir + "/start_1");
     const jsonmini::Value j = jsonmini::Parser::parse(std::string(hdr.begin(), hdr.end()));
@@ -277,6 +281,10 @@ static int cmd_stream2nxs(const std::string& dir, const std::string& prefix, siz
         if (!links) w.save(prefix + suffix);
         VdsMapping m;
         m.file = base + suffix, m.dataset = "/data";
+        if (external) {
+            Writer::external_link(master.group("/entry/data"), dname, base + suffix, "/data");
+            m.file = ".", m.dataset = std::string("/entry/data/") + dname;
+        }
         m.src_start = {0, 0, 0}, m.src_block = {cnt, H, W};
         m.dst_start = {f0, 0, 0}, m.dst_block = {cnt, H, W};
         maps.push_back(m);

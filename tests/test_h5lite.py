@@ -451,7 +451,7 @@ def make_scan(tmp_path, dtype=np.uint16, bits=16, n=7, per_file=3, mode="", omeg
     return frames, mask
 
 
-@pytest.mark.parametrize("mode", ["", "links"])
+@pytest.mark.parametrize("mode", ["", "links", "external"])
 def test_h5read_metadata_and_chunks(tmp_path, mode):
     frames, mask = make_scan(tmp_path, mode=mode)
     info, out, err = h5read(tmp_path / "scan.nxs")
@@ -526,3 +526,23 @@ def test_h5read_rejects_what_it_cannot_serve(tmp_path):
     (tmp_path / "scan_000002.h5").write_bytes((other / "scan_000001.h5").read_bytes())
     r = tool("h5read", tmp_path / "scan.nxs", check=False)
     assert r.returncode == 1 and b"Validation Error" in r.stderr and b"fast data has 80 pixels, expected 96" in r.stderr
+
+
+def test_external_links_both_parsers(tmp_path):
+    """The master of `stream2nxs ... external`: /entry/data is a compact (link-message) group holding
+    external links; the VDS names its sources as file "." + those links (h5read.c:945-985)."""
+    frames, mask = make_scan(tmp_path, mode="external")
+    m = h5dissect.File(tmp_path / "scan.nxs")
+    links = m.get("/entry/data").links()
+    assert links["data_000002"] == ("external", "scan_000002.h5", "/data") and links["data"][0] == "hard"
+    d = dump(tmp_path / "scan.nxs")["objects"]["/entry/data"]["links"]
+    assert d["data_000003"] == {"external": ["scan_000003.h5", "/data"]} and "hard" in d["data"]
+    maps = json.loads(tool("vds", tmp_path / "scan.nxs", "/entry/data/data").stdout)
+    assert [(x["file"], x["dataset"]) for x in maps] == [(".", f"/entry/data/data_{k:06d}") for k in (1, 2, 3)]
+    # the C++ resolver follows the link into the other file
+    want = compress_chunk(frames[4])
+    assert tool("chunk", tmp_path / "scan.nxs", "/entry/data/data_000002", 1, 0, 0).stdout == want
+    # a data file that is missing: frames behind its link poll as not available
+    (tmp_path / "scan_000003.h5").unlink()
+    info, _, _ = h5read(tmp_path / "scan.nxs")
+    assert info["available"][6] == 0 and all(info["available"][:6])
