@@ -17,7 +17,7 @@
 // reference's tests expect from the latter (tests/test_h5lite.py).
 //
 // Reader: superblock 0-3; object headers 1 and 2; symbol-table groups, compact link messages
-// (hard / soft / external), dense link storage is refused with a clear message; dataspace 1/2;
+// (hard / soft / external), dense link storage (fractal heap + version 2 B-tree); dataspace 1/2;
 // fixed, float, string, variable-length string, enum datatypes; layout 3 and 4: compact,
 // contiguous, chunked (version 1 B-tree, single chunk, implicit, fixed array, extensible
 // array), virtual (VDS mapping list with regular hyperslabs); filter pipeline 1/2; attribute
@@ -56,6 +56,13 @@ inline void wr_le(uint8_t* p, uint64_t v, int n) {
     for (int i = 0; i < n; ++i) p[i] = (uint8_t)(v >> (8 * i));
 }
 inline uint64_t pad8(uint64_t n) { return (n + 7) & ~7ull; }
+namespace detail {
+inline unsigned log2_floor(uint64_t v) {
+    unsigned r = 0;
+    while (v >>= 1) ++r;
+    return r;
+}
+}  // namespace detail
 
 // ------------------------------------------------------------------------------------------
 // Datatypes
@@ -640,6 +647,145 @@ inline bool parse_link_message(const std::vector<uint8_t>& d, std::string& name,
 }
 }  // namespace detail
 
+// ---- dense link storage: fractal heap + version 2 B-tree ---------------------------------
+// New-format groups with more than 8 links keep their link messages as objects of a fractal
+// heap ("FRHP"; direct blocks "FHDB", indirect blocks "FHIB") and index them by name hash in a
+// version 2 B-tree ("BTHD" / "BTIN" / "BTLF", record type 5 = {hash u32, heap id}).  Every
+// record of the tree is visited (no hash lookup), each heap id is resolved to the link message.
+namespace detail {
+struct FractalHeap {
+    const File& f;
+    unsigned id_len = 0, table_width = 0, max_heap_bits = 0, cur_rows = 0, off_bytes = 0, len_bytes = 0;
+    uint64_t start_block = 0, max_direct = 0, root = UNDEF;
+    bool filtered = false, block_checksum = false;
+
+    FractalHeap(const File& file, uint64_t addr) : f(file) {
+        const uint8_t* h = f.at(addr, 142);
+        if (memcmp(h, "FRHP", 4) != 0 || h[4] != 0) throw Error("h5lite: fractal heap header");
+        id_len = (unsigned)rd_le(h + 5, 2);
+        filtered = rd_le(h + 7, 2) != 0;
+        block_checksum = h[9] & 2;
+        const uint64_t max_managed = rd_le(h + 10, 4);
+        table_width = (unsigned)rd_le(h + 110, 2);
+        start_block = rd_le(h + 112, 8), max_direct = rd_le(h + 120, 8);
+        max_heap_bits = (unsigned)rd_le(h + 128, 2);
+        root = rd_le(h + 132, 8);
+        cur_rows = (unsigned)rd_le(h + 140, 2);
+        if (!table_width || !start_block || start_block > max_direct || max_heap_bits > 64)
+            throw Error("h5lite: fractal heap parameters");
+        if (filtered) throw Error("h5lite: filtered fractal heaps are not handled");
+        off_bytes = (max_heap_bits + 7) / 8;
+        const uint64_t lim = std::min(max_direct, max_managed);
+        len_bytes = (log2_floor(lim) / 8) + 1;
+    }
+    unsigned block_header() const { return 5 + 8 + off_bytes + (block_checksum ? 4 : 0); }
+    uint64_t row_block_size(unsigned row) const { return row < 2 ? start_block : start_block << (row - 1); }
+    unsigned max_direct_rows() const { return log2_floor(max_direct) - log2_floor(start_block) + 2; }
+
+    // File address of heap offset `off` (length len) below the block at `addr` whose first heap
+    // offset is `base`; rows > 0: indirect block of that many rows, rows == 0: direct block of `size`.
+    const uint8_t* locate(uint64_t addr, unsigned rows, uint64_t size, uint64_t base, uint64_t off, uint64_t len,
+                          int depth) const {
+        if (addr == UNDEF) throw Error("h5lite: fractal heap object in an unallocated block");
+        if (depth > 16) throw Error("h5lite: fractal heap too deep");
+        if (rows == 0) {
+            if (memcmp(f.at(addr, 4), "FHDB", 4) != 0) throw Error("h5lite: fractal heap direct block signature");
+            if (off < base || off - base + len > size) throw Error("h5lite: fractal heap object outside its block");
+            return f.at(addr + (off - base), len);
+        }
+        if (memcmp(f.at(addr, 4), "FHIB", 4) != 0) throw Error("h5lite: fractal heap indirect block signature");
+        const uint64_t entries = addr + 5 + 8 + off_bytes;
+        const unsigned mdr = max_direct_rows();
+        uint64_t cur = base;
+        for (unsigned r = 0; r < rows; ++r) {
+            const uint64_t bs = row_block_size(r);
+            for (unsigned c = 0; c < table_width; ++c) {
+                const unsigned k = r * table_width + c;
+                if (off >= cur && off - cur < bs) {
+                    const uint64_t child = rd_le(f.at(entries + 8ull * k, 8), 8);
+                    if (r < mdr) return locate(child, 0, bs, cur, off, len, depth + 1);
+                    // an indirect child covering bs bytes: its row count follows from its size
+                    const unsigned child_rows = log2_floor(bs) - log2_floor(start_block * table_width) + 1;
+                    return locate(child, child_rows, 0, cur, off, len, depth + 1);
+                }
+                cur += bs;
+            }
+        }
+        throw Error("h5lite: fractal heap offset beyond the root block");
+    }
+
+    std::vector<uint8_t> object(const uint8_t* id) const {
+        if ((id[0] >> 6) != 0) throw Error("h5lite: fractal heap id version");
+        const unsigned type = (id[0] >> 4) & 3;
+        if (type == 2) {  // tiny: the object is inside the id
+            const unsigned n = (id[0] & 15) + 1;
+            return std::vector<uint8_t>(id + 1, id + 1 + std::min(n, id_len - 1));
+        }
+        if (type != 0) throw Error("h5lite: huge fractal heap objects are not handled");
+        if (1 + off_bytes + len_bytes > id_len) throw Error("h5lite: fractal heap id length");
+        const uint64_t off = rd_le(id + 1, (int)off_bytes), len = rd_le(id + 1 + off_bytes, (int)len_bytes);
+        const uint8_t* p = cur_rows ? locate(root, cur_rows, 0, 0, off, len, 0) : locate(root, 0, start_block, 0, off, len, 0);
+        return std::vector<uint8_t>(p, p + len);
+    }
+};
+
+// Calls visit(record) for every record of a version 2 B-tree.
+template <class F>
+inline void btree_v2_records(const File& f, uint64_t addr, F&& visit) {
+    const uint8_t* h = f.at(addr, 34);
+    if (memcmp(h, "BTHD", 4) != 0 || h[4] != 0) throw Error("h5lite: version 2 B-tree header");
+    const uint64_t node_size = rd_le(h + 6, 4), rec = rd_le(h + 10, 2);
+    const unsigned depth = (unsigned)rd_le(h + 12, 2);
+    const uint64_t root = rd_le(h + 16, 8);
+    const unsigned root_nrec = (unsigned)rd_le(h + 24, 2);
+    if (!rec || node_size < 16 || depth > 8) throw Error("h5lite: version 2 B-tree parameters");
+    if (root == UNDEF || root_nrec == 0) return;
+    // node_info as H5B2hdr.c builds it: records per node and the width of the counters in child pointers
+    std::vector<uint64_t> max_nrec(depth + 1), cum_max(depth + 1);
+    std::vector<unsigned> cum_size(depth + 1, 0);
+    max_nrec[0] = (node_size - 10) / rec;
+    cum_max[0] = max_nrec[0];
+    const unsigned nrec_size = log2_floor(max_nrec[0]) / 8 + 1;
+    for (unsigned u = 1; u <= depth; ++u) {
+        const uint64_t ptr = 8 + nrec_size + cum_size[u - 1];
+        max_nrec[u] = (node_size - (10 + ptr)) / (rec + ptr);
+        cum_max[u] = (max_nrec[u] + 1) * cum_max[u - 1] + max_nrec[u];
+        cum_size[u] = log2_floor(cum_max[u]) / 8 + 1;
+    }
+    struct Walk {
+        const File& f;
+        uint64_t rec;
+        unsigned nrec_size;
+        const std::vector<unsigned>& cum_size;
+        F& visit;
+        void node(uint64_t a, unsigned nrec, unsigned d) {
+            const uint8_t* n = f.at(a, 6 + (uint64_t)nrec * rec);
+            if (memcmp(n, d ? "BTIN" : "BTLF", 4) != 0) throw Error("h5lite: version 2 B-tree node signature");
+            for (unsigned i = 0; i < nrec; ++i) visit(n + 6 + i * rec);
+            if (!d) return;
+            const uint64_t ptr = 8 + nrec_size + (d > 1 ? cum_size[d - 1] : 0);
+            const uint64_t p0 = a + 6 + (uint64_t)nrec * rec;
+            for (unsigned i = 0; i <= nrec; ++i) {
+                const uint8_t* p = f.at(p0 + i * ptr, ptr);
+                node(rd_le(p, 8), (unsigned)rd_le(p + 8, (int)nrec_size), d - 1);
+            }
+        }
+    } w{f, rec, nrec_size, cum_size, visit};
+    w.node(root, root_nrec, depth);
+}
+
+inline void dense_links(const File& f, uint64_t heap_addr, uint64_t btree_addr, std::map<std::string, Link>& out) {
+    const FractalHeap heap(f, heap_addr);
+    if (btree_addr == UNDEF) throw Error("h5lite: dense link storage without a name index");
+    btree_v2_records(f, btree_addr, [&](const uint8_t* rec) {
+        const auto msg = heap.object(rec + 4);  // {hash u32, heap id}
+        std::string name;
+        Link l;
+        if (parse_link_message(msg, name, l)) out[name] = l;
+    });
+}
+}  // namespace detail
+
 inline std::map<std::string, Link> Object::links() const {
     std::map<std::string, Link> out;
     if (const Message* st = first(0x11)) {
@@ -656,9 +802,8 @@ inline std::map<std::string, Link> Object::links() const {
     if (const Message* li = first(0x02)) {
         const uint8_t flags = li->data.at(1);
         const size_t p = 2 + ((flags & 1) ? 8 : 0);
-        if (p + 8 <= li->data.size() && rd_le(&li->data[p], 8) != UNDEF)
-            throw Error("h5lite: " + f_->path() + ": this group keeps its links in a fractal heap (dense storage, "
-                        "more than 8 links in a new-format group), which this reader does not handle");
+        if (p + 16 <= li->data.size() && rd_le(&li->data[p], 8) != UNDEF)
+            detail::dense_links(*f_, rd_le(&li->data[p], 8), rd_le(&li->data[p + 8], 8), out);
     }
     return out;
 }
@@ -906,8 +1051,9 @@ inline std::map<std::string, Attribute> Object::attributes() const {
     if (const Message* ai = first(0x15)) {
         const uint8_t flags = ai->data.at(1);
         const size_t p = 2 + ((flags & 1) ? 2 : 0);
-        if (p + 8 <= ai->data.size() && rd_le(&ai->data[p], 8) != UNDEF)
-            throw Error("h5lite: attributes kept in a fractal heap (dense storage) are not handled");
+        // attributes in dense storage (fractal heap): nothing on this path reads attributes of such
+        // objects; they are left out rather than refused
+        (void)p;
     }
     return out;
 }
@@ -946,12 +1092,6 @@ inline std::vector<std::string> decode_strings(const File& f, const Datatype& dt
 
 // ---- chunk lookup ------------------------------------------------------------------------
 namespace detail {
-inline unsigned log2_floor(uint64_t v) {
-    unsigned r = 0;
-    while (v >>= 1) ++r;
-    return r;
-}
-
 // Version 1 B-tree, node type 1 (raw data chunks): keys are {size u32, filter mask u32,
 // offsets u64[rank + 1]}; child i of a node covers key[i] <= offset < key[i + 1].
 inline ChunkInfo btree_v1_chunk(const File& f, uint64_t addr, const std::vector<uint64_t>& offset, int depth) {

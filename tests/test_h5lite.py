@@ -546,3 +546,95 @@ def test_external_links_both_parsers(tmp_path):
     (tmp_path / "scan_000003.h5").unlink()
     info, _, _ = h5read(tmp_path / "scan.nxs")
     assert info["available"][6] == 0 and all(info["available"][:6])
+
+
+@pytest.mark.parametrize("layout", ["root-direct", "root-indirect"])
+def test_dense_link_storage(tmp_path, layout):
+    """A new-format group with more than 8 links: link messages live in a fractal heap and are
+    indexed by a version 2 B-tree (what a libver='latest' / SWMR writer produces for e.g.
+    /entry/instrument/detector).  Built here from the format specification: 30 hard links,
+    heap with a direct root block / with a two-row indirect root block, B-tree of depth 0 / 1."""
+    src = tmp_path / "s.h5"
+    tool("write-stress", src)
+    f = h5dissect.File(src)
+    buf = bytearray(f.buf)
+    targets = {f"f{i:02d}": f.get(f"/many/d{i * 7:03d}").addr for i in range(30)}
+    msgs = {n: bytes([1, 0, len(n)]) + n.encode() + struct.pack("<Q", a) for n, a in targets.items()}
+
+    base = len(buf)
+    ohdr_addr = base
+    heap_addr = ohdr_addr + 64
+    bt_addr = heap_addr + 160
+    blocks_addr = bt_addr + 64
+    # --- fractal heap: objects packed behind each direct block's 21-byte prefix
+    hdr_len = 5 + 8 + 4 + 4
+    names = sorted(msgs)
+    if layout == "root-direct":
+        placement = {0: names}                                   # block index -> names
+        cur_rows = 0
+    else:
+        placement = {0: names[:12], 1: names[12:20], 5: names[20:]}   # row 0: blocks 0-3, row 1: blocks 4-7
+        cur_rows = 2
+    ids, direct = {}, {}
+    for k, ns in placement.items():
+        data = b""
+        for n in ns:
+            off = k * 512 + hdr_len + len(data)
+            ids[n] = bytes([0]) + struct.pack("<I", off) + struct.pack("<H", len(msgs[n]))
+            data += msgs[n]
+        blk = b"FHDB" + bytes([0]) + struct.pack("<Q", heap_addr) + struct.pack("<I", k * 512) + bytes(4) + data
+        direct[k] = blk + bytes(512 - len(blk))
+    layout_bytes = b""
+    block_addr = {}
+    for k in sorted(direct):
+        block_addr[k] = blocks_addr + len(layout_bytes)
+        layout_bytes += direct[k]
+    if cur_rows:
+        iblk_addr = blocks_addr + len(layout_bytes)
+        iblk = b"FHIB" + bytes([0]) + struct.pack("<Q", heap_addr) + struct.pack("<I", 0)
+        iblk += b"".join(struct.pack("<Q", block_addr.get(k, h5dissect.UNDEF)) for k in range(8)) + bytes(4)
+        layout_bytes += iblk
+        root = iblk_addr
+    else:
+        root = block_addr[0]
+    heap = b"FRHP" + bytes([0]) + struct.pack("<HHB", 7, 0, 2) + struct.pack("<I", 4096)
+    heap += struct.pack("<12Q", 0, h5dissect.UNDEF, 0, h5dissect.UNDEF, 0, 0, 0, 30, 0, 0, 0, 0)
+    heap += struct.pack("<HQQHH", 4, 512, 65536, 32, 1) + struct.pack("<QH", root, cur_rows) + bytes(4)
+    assert len(heap) == 146
+    # --- version 2 B-tree, record type 5: {hash u32 (not used by the reader), heap id (7 bytes)}
+    rec = lambda n: bytes(4) + ids[n]
+    nodes_addr = blocks_addr + len(layout_bytes)
+    if layout == "root-direct":
+        leaf = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in names) + bytes(4)
+        nodes = leaf
+        bt_root, root_nrec, depth = nodes_addr, 30, 0
+    else:
+        left, mid, right = names[:15], names[15], names[16:]
+        leaf1 = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in left) + bytes(4)
+        leaf2 = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in right) + bytes(4)
+        a1, a2 = nodes_addr, nodes_addr + len(leaf1)
+        internal = b"BTIN" + bytes([0, 5]) + rec(mid) + struct.pack("<QB", a1, len(left)) + struct.pack("<QB", a2, len(right)) + bytes(4)
+        nodes = leaf1 + leaf2 + internal
+        bt_root, root_nrec, depth = a2 + len(leaf2), 1, 1
+    bt = b"BTHD" + bytes([0, 5]) + struct.pack("<IHHBB", 512, 11, depth, 100, 40) + struct.pack("<QHQ", bt_root, root_nrec, 30) + bytes(4)
+    # --- the group's object header (version 2): link info + group info
+    linfo = bytes([0, 0]) + struct.pack("<QQ", heap_addr, bt_addr)
+    body = bytes([2]) + struct.pack("<H", len(linfo)) + bytes([0]) + linfo + bytes([10]) + struct.pack("<H", 2) + bytes([1, 0, 0])
+    ohdr = b"OHDR" + bytes([2, 0, len(body)]) + body + bytes(4)
+    assert len(ohdr) <= 64 and len(heap) <= 160 and len(bt) <= 64
+    buf += ohdr + bytes(64 - len(ohdr)) + heap + bytes(160 - len(heap)) + bt + bytes(64 - len(bt)) + layout_bytes + nodes
+    # --- hang it where /links was
+    old = struct.pack("<Q", f.get("/links").addr)
+    snod_hits = [i for i in range(len(f.buf) - 8) if f.buf[i:i + 8] == old]
+    assert len(snod_hits) == 1
+    buf[snod_hits[0]:snod_hits[0] + 8] = struct.pack("<Q", ohdr_addr)
+    struct.pack_into("<I", buf, snod_hits[0] + 8, 0)  # cache type 0: nothing cached in the entry
+    struct.pack_into("<Q", buf, 40, len(buf))
+    out = tmp_path / f"dense_{layout}.h5"
+    out.write_bytes(buf)
+
+    d = dump(out)["objects"]
+    assert sorted(d["/links"]["links"]) == names
+    assert {n: v["hard"] for n, v in d["/links"]["links"].items()} == targets
+    for i in (0, 11, 12, 19, 20, 29):
+        assert cat(out, f"/links/f{i:02d}", "<i4").tolist() == [i * 7, -i * 7]
