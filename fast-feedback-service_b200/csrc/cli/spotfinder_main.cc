@@ -17,6 +17,7 @@
 #include "png_writer.hpp"
 #include "reader.hpp"
 #include "reader_h5.hpp"
+#include "reader_sample.hpp"
 #include "h5_results.hpp"
 
 #ifndef FFS_VERSION
@@ -117,10 +118,13 @@ int main(int argc, char** argv) {
 
     // ---- reader ---------------------------------------------------------------------------
     const std::string& file = args.file;
-    if (!std::filesystem::exists(file))
+    const bool sample = file.empty();  // --sample, or no file with H5READ_IMPLICIT_SAMPLE set (args.hpp)
+    if (!sample && !std::filesystem::exists(file))
         wait_for_ready(file, [](const std::string& s) { return std::filesystem::exists(s); }, args.timeout);
     std::unique_ptr<Reader> reader_ptr;
-    if (std::filesystem::is_directory(file)) {
+    if (sample) {
+        reader_ptr = std::make_unique<SampleRead>(sizeof(pixel_t));
+    } else if (std::filesystem::is_directory(file)) {
         wait_for_ready(file, SHMRead::is_ready_for_read, args.timeout);
         try {
             reader_ptr = std::make_unique<SHMRead>(file);

@@ -169,3 +169,71 @@ def test_save_h5_rotation_from_nxs(tmp_path):
     assert np.array_equal(col("spot_extent_z"), depth)
     assert np.allclose(col("sigma_b_variance"), sb, rtol=1e-4, atol=1e-12)
     assert np.allclose(col("sigma_m_variance"), sm, rtol=1e-4, atol=1e-12)
+
+
+def sample_frames(dtype):
+    """The six frames of h5read's --sample source (h5read.c:203-276), rebuilt with numpy; frame 5's
+    pcg32 stream comes from jump-ahead doubling of the LCG (state_k = A_k * s0 + C_k mod 2^64)."""
+    MOD_FAST, MOD_SLOW, GAP_FAST, GAP_SLOW, SLOW, FAST = 1028, 512, 12, 38, 4362, 4148
+    mask = np.ones((SLOW, FAST), np.uint8)
+    for gap in range(1, 8):
+        y = gap * MOD_SLOW + (gap - 1) * GAP_SLOW
+        mask[y:y + GAP_SLOW] = 0
+    for gap in range(1, 4):
+        x = gap * MOD_FAST + (gap - 1) * GAP_FAST
+        mask[:, x:x + GAP_FAST] = 0
+    frames = np.zeros((6, SLOW, FAST), dtype)
+    frames[1][mask != 0] = 1
+    frames[2][::42, ::42] = 100
+    frames[3] = np.arange(FAST, dtype=dtype)[None, :]
+    frames[4] = np.arange(SLOW, dtype=dtype)[:, None]
+    n = 8 * 4 * MOD_SLOW * MOD_FAST
+    mult = np.uint64(6364136223846793005)
+    with np.errstate(over="ignore"):
+        A, C = np.array([1], np.uint64), np.array([0], np.uint64)   # state before draw k, from s0 = 0, inc | 1 = 1
+        while len(A) < n:
+            An, Cn = A[-1] * mult, C[-1] * mult + np.uint64(1)      # one step past the last known
+            A, C = np.concatenate([A, A * An]), np.concatenate([C, A * Cn + C])
+        old = C[:n]
+        xs = (((old >> np.uint64(18)) ^ old) >> np.uint64(27)).astype(np.uint32)
+        rot = (old >> np.uint64(59)).astype(np.uint32)
+        draws = (xs >> rot) | (xs << ((np.uint32(0) - rot) & np.uint32(31)))
+    vals = (draws % np.uint32(10)).astype(dtype).reshape(8, 4, MOD_SLOW, MOD_FAST)
+    for my in range(8):
+        for mx in range(4):
+            r0, c0 = my * (MOD_SLOW + GAP_SLOW), mx * (MOD_FAST + GAP_FAST)
+            frames[5][r0:r0 + MOD_SLOW, c0:c0 + MOD_FAST] = vals[my, mx]
+    return frames, mask
+
+
+def test_pcg32_stream_of_the_sample_generator():
+    # first outputs of pcg32 with state = 0, inc = 0 (h5read.c:189-201), stepped one at a time
+    state, out = 0, []
+    for _ in range(5):
+        old = state
+        state = (old * 6364136223846793005 + 1) & (2**64 - 1)
+        xs = (((old >> 18) ^ old) >> 27) & 0xFFFFFFFF
+        rot = old >> 59
+        out.append(((xs >> rot) | (xs << ((-rot) & 31))) & 0xFFFFFFFF)
+    frames, _ = sample_frames(np.uint16)
+    assert frames[5][0, :5].tolist() == [v % 10 for v in out]
+
+
+@pytest.mark.parametrize("exe,dtype", [("spotfinder", np.uint16), ("spotfinder32", np.uint32)])
+def test_sample_source(exe, dtype, tmp_path):
+    frames, mask = sample_frames(dtype)
+    rc, lines, out, err = run(exe, ["--sample", "--threads", "3"], timeout=300, cwd=tmp_path)
+    assert rc == 0 and err == "", out + err
+    assert sorted(l["file-number"] for l in lines) == list(range(6))
+    for l in lines:
+        i = l["file-number"]
+        strong = oracle.dispersion(frames[i], mask)
+        _, spots = oracle.connected_components(strong, frames[i], want_labels=False)
+        assert l["num_strong_pixels"] == int(strong.sum()), i
+        assert l["n_spots_total"] == int((spots["num_pixels"] >= 3).sum()), i
+    by = {l["file-number"]: l for l in lines}
+    assert by[0]["num_strong_pixels"] == 0 and by[1]["num_strong_pixels"] == 0   # flat frames have no spots
+    assert by[2]["num_strong_pixels"] > 0                                        # the 100-count pixels
+    # the file group is required unless the environment says otherwise (spotfinder.cc:266-282)
+    rc, _, out, _ = run(exe, [])
+    assert rc == 1 and "One of the arguments '--sample' or 'FILE.nxs' is required" in out
