@@ -191,6 +191,121 @@ def refgpu_resolution_mask(mask, wavelength, distance_m, bcx_px, bcy_px, psx_m, 
     return out
 
 
+class RefCCSpot(C.Structure):
+    _fields_ = [("x_min", C.c_uint32), ("x_max", C.c_uint32), ("y_min", C.c_uint32), ("y_max", C.c_uint32),
+                ("z_min", C.c_int32), ("z_max", C.c_int32), ("num_pixels", C.c_int32), ("depth", C.c_int32),
+                ("com_x", C.c_float), ("com_y", C.c_float), ("com_z", C.c_float), ("pad", C.c_float),
+                ("sigma_b_variance", C.c_double), ("sigma_m_variance", C.c_double)]
+
+
+class RefCCBox(C.Structure):
+    _fields_ = [("l", C.c_uint32), ("t", C.c_uint32), ("r", C.c_uint32), ("b", C.c_uint32), ("num_pixels", C.c_int32)]
+
+
+REFCC_SPOT_DTYPE = np.dtype(RefCCSpot)
+REFCC_BOX_DTYPE = np.dtype(RefCCBox)
+_REFCC = {}
+
+
+def refcc_available(bytes_per_pixel: int = 2) -> bool:
+    return (_HERE / ("_ref/libffs_refcc.so" if bytes_per_pixel == 2 else "_ref/libffs_refcc32.so")).exists()
+
+
+def refcc(bytes_per_pixel: int = 2) -> C.CDLL:
+    """The reference's own host-side ConnectedComponents / Reflection3D / filter_reflections /
+    variances_in_kabsch_space (spotfinder/connected_components/connected_components.cc, dx2 Panel
+    and Scan) compiled in place behind oracle/refcc_shim.cc (stand-in Boost.Graph / Eigen:
+    oracle/stub_cc)."""
+    if bytes_per_pixel not in _REFCC:
+        name = "_ref/libffs_refcc.so" if bytes_per_pixel == 2 else "_ref/libffs_refcc32.so"
+        G = C.CDLL(str(_HERE / name))
+        G.ffs_refcc_new.restype = C.c_void_p
+        G.ffs_refcc_free.argtypes = [C.c_void_p]
+        G.ffs_refcc_add_slice.restype = C.c_int
+        G.ffs_refcc_add_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                          C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        G.ffs_refcc_boxes.restype = C.c_int
+        G.ffs_refcc_boxes.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+        G.ffs_refcc_find_2d.restype = C.c_long
+        G.ffs_refcc_find_2d.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_float, C.c_void_p, C.c_size_t,
+                                        C.POINTER(C.c_uint32)]
+        G.ffs_refcc_find_3d.restype = C.c_long
+        G.ffs_refcc_find_3d.argtypes = [C.c_void_p, C.c_uint32, C.c_float, C.c_void_p, C.c_size_t]
+        G.ffs_refcc_variances.restype = C.c_long
+        G.ffs_refcc_variances.argtypes = [C.c_void_p] + [C.c_double] * 8 + [C.c_int, C.c_void_p, C.c_size_t]
+        assert G.ffs_refcc_pixel_bytes() == bytes_per_pixel
+        _REFCC[bytes_per_pixel] = G
+    return _REFCC[bytes_per_pixel]
+
+
+class RefCC:
+    """One run of the reference's connected-components code over a frame or a sweep.
+
+        with RefCC(frames, strong, min_spot_size=3) as r:      # (Z, H, W) or (H, W)
+            r.num_strong, r.num_strong_filtered, r.boxes       # per slice (get_boxes())
+            r.find_2d(slice, 3, 2.0)  -> (spots after both filters, components before)
+            r.find_3d(3, 2.0)         -> spots after both filters, in the reference's order
+            r.variances(geometry)     -> the same spots with sigma_b / sigma_m variances and depth
+    """
+
+    def __init__(self, frames, strong, min_spot_size=3):
+        frames = np.ascontiguousarray(frames)
+        strong = np.ascontiguousarray(strong, dtype=np.uint8)
+        if frames.ndim == 2:
+            frames, strong = frames[None], strong[None]
+        assert frames.shape == strong.shape and frames.dtype in (np.uint16, np.uint32)
+        self.G = refcc(frames.dtype.itemsize)
+        self.h = self.G.ffs_refcc_new()
+        self.n_images = len(frames)
+        self.cap = max(int(np.count_nonzero(strong)), 1)
+        self.num_strong, self.num_strong_filtered, self.boxes = [], [], []
+        z, hgt, w = frames.shape
+        for f, s in zip(frames, strong):
+            a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+            idx = self.G.ffs_refcc_add_slice(self.h, s.ctypes.data, f.ctypes.data, w, hgt, min_spot_size,
+                                             C.byref(a), C.byref(b), C.byref(c))
+            if idx < 0:
+                raise RuntimeError("reference ConnectedComponents threw")
+            boxes = np.zeros(max(c.value, 1), REFCC_BOX_DTYPE)
+            self.G.ffs_refcc_boxes(self.h, idx, boxes.ctypes.data, len(boxes))
+            self.num_strong.append(a.value)
+            self.num_strong_filtered.append(b.value)
+            self.boxes.append(boxes[:c.value].copy())
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.G.ffs_refcc_free(self.h)
+        self.h = None
+
+    def find_2d(self, slice_index, min_spot_size=3, max_sep=2.0):
+        out = np.zeros(self.cap, REFCC_SPOT_DTYPE)
+        before = C.c_uint32()
+        n = self.G.ffs_refcc_find_2d(self.h, slice_index, min_spot_size, max_sep, out.ctypes.data, len(out), C.byref(before))
+        if n < 0:
+            raise RuntimeError("reference find_2d_components threw")
+        return out[:n].copy(), before.value
+
+    def find_3d(self, min_spot_size=3, max_sep=2.0):
+        out = np.zeros(self.cap, REFCC_SPOT_DTYPE)
+        n = self.G.ffs_refcc_find_3d(self.h, min_spot_size, max_sep, out.ctypes.data, len(out))
+        if n < 0:
+            raise RuntimeError("reference find_3d_components threw")
+        self._last = out[:n].copy()
+        return self._last.copy()
+
+    def variances(self, geometry, oscillation_start=0.0):
+        g = geometry
+        out = self._last.copy()
+        n = self.G.ffs_refcc_variances(self.h, g["distance_mm"], g["beam_center_x_px"], g["beam_center_y_px"],
+                                       g["pixel_size_x_mm"], g["pixel_size_y_mm"], g["wavelength"], oscillation_start,
+                                       g["oscillation_width_deg"], self.n_images, out.ctypes.data, len(out))
+        if n < 0:
+            raise RuntimeError("reference variances_in_kabsch_space threw")
+        return out
+
+
 def default_params(**kw) -> OracleParams:
     p = OracleParams()
     lib().ffs_oracle_default_params(C.byref(p))
