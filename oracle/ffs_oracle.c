@@ -8,10 +8,10 @@
  * every double operation is a separately rounded IEEE-754 operation, exactly as
  * in the reference's x86-64 build.
  *
- * Parity status: standard dispersion PINNED against oracle/_ref (the reference's
- * standalone.cc compiled in place) and tests/golden/; dispersion_extended and
- * connected components "parity unpinned" (DIALS / Boost absent) -- see
- * ffs_oracle.h and DESIGN.md.
+ * Parity status: every part is PINNED against the reference's own sources compiled in
+ * place under oracle/_ref/ -- standard dispersion: standalone.cc (+ tests/golden/);
+ * dispersion_extended and the gain variants: baseline.cpp; connected components, spots,
+ * filters, 3D components: connected_components.cc -- see ffs_oracle.h and DESIGN.md 6.
  */
 #include "ffs_oracle.h"
 
@@ -212,8 +212,7 @@ int64_t ffs_oracle_dispersion(const void *image, int bpp, const uint8_t *mask, i
  * src, mask, gain, dst) :187-250: same SAT, per-pixel gain map,
  *     a = m*y - x*x;  b = m*src - x;
  *     c = gain*x*(m - 1 + nsig_b*sqrt(2*(m - 1)));  d = nsig_s*sqrt(gain*x*m);
- * PARITY UNPINNED (baseline.cpp needs DIALS/scitbx headers; no executable of the reference
- * reaches this variant). */
+ * Pinned bit for bit against the reference's own class (tests/test_oracle_refext.py). */
 int64_t ffs_oracle_dispersion_gain(const void *image, int bpp, const uint8_t *mask, int width,
                                    int height, const ffs_oracle_params *p, const double *gain,
                                    uint8_t *dst) {
@@ -392,7 +391,7 @@ int64_t ffs_oracle_dispersion_extended(const void *image, int bpp, const uint8_t
 }
 
 /* DispersionExtendedThreshold::threshold_w_gain, baseline.cpp:772-805.  stage as in
- * ffs_oracle_extended_stage.  PARITY UNPINNED (see the header). */
+ * ffs_oracle_extended_stage.  Pinned stage by stage (tests/test_oracle_refext.py). */
 int64_t ffs_oracle_dispersion_extended_gain(const void *image, int bpp, const uint8_t *mask,
                                             int width, int height, const ffs_oracle_params *p,
                                             const double *gain, int stage, uint8_t *dst) {

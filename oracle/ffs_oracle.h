@@ -12,13 +12,19 @@
  *     reference's own baseline/spotfinder/standalone.cc compiled in place
  *     (oracle/_ref/libffs_ref.so) and against tests/golden/ fixtures produced
  *     by it.
- *   - dispersion_extended : parity unpinned -- baseline.cpp needs DIALS/scitbx
- *     headers which are absent; restated from baseline.cpp:325-813 and
- *     cross-checked by (a) pass 1 + "b > d" == standard dispersion and
- *     (b) a brute-force window-sum implementation.
- *   - connected components: parity unpinned -- Boost.Graph absent; restated
- *     from connected_components.cc and cross-checked against
- *     scipy.ndimage.label.
+ *   - dispersion_extended and the gain-map variants of both algorithms : PINNED
+ *     -- checked bit for bit, stage by stage, against the reference's own
+ *     baseline/spotfinder/baseline.cpp classes compiled in place
+ *     (oracle/_ref/libffs_refext.so; scitbx array views and DIALS's
+ *     chebyshev_distance are the stand-ins of oracle/stub_dials, the latter
+ *     also checked against scipy's chessboard distance transform).
+ *   - connected components, spot fields, the two filters, 3D components,
+ *     Kabsch-space variances : PINNED -- same spots, same order, same floats
+ *     as the reference's own connected_components.cc + dx2 Panel / Scan
+ *     compiled in place (oracle/_ref/libffs_refcc*.so; Boost.Graph and Eigen
+ *     are the stand-ins of oracle/stub_cc).
+ *   Both pins need /root/reference at build time; tests/test_oracle_refext.py
+ *   and tests/test_oracle_refcc.py skip where the built libraries are absent.
  */
 #ifndef FFS_ORACLE_H
 #define FFS_ORACLE_H

@@ -510,9 +510,8 @@ def process_frame(image, mask, params=None, algorithm=ALGO_DISPERSION, min_spot_
 
 def kabsch_variances(labels, image, spots, geometry):
     """Reflection3D::variances_in_kabsch_space (connected_components.cc:159-203) driven as the
-    caller loop does (spotfinder.cc:1157-1196), restated pixel by pixel in fp64 -- PARITY
-    UNPINNED: the reference's own check (tests/test_spotfinder.py:108-114) needs a dataset that
-    is not in the tree, and dx2 / Eigen are not available to compile the original here.
+    caller loop does (spotfinder.cc:1157-1196), restated pixel by pixel in fp64.  Pinned against
+    the reference's own function (RefCC.variances, tests/test_oracle_refcc.py: 1e-12 relative).
 
     labels/image: (Z, H, W) from connected_components(); spots: its records (com_* as float32,
     the reference's center_of_mass() type).  geometry: dict with the ffs_kabsch_geometry keys.

@@ -32,7 +32,7 @@ def test_oracle_matches_live_reference(dtype):
 
 
 def test_extended_self_checks():
-    """dispersion_extended is unpinned offline (baseline.cpp needs DIALS headers): the SAT
+    """Besides the pin against the reference's own baseline.cpp (tests/test_oracle_refext.py): the SAT
     restatement must equal the brute-force one, and its first pass AND-ed with the signal
     test must reproduce the (pinned) standard dispersion."""
     for seed, (h, w) in enumerate([(90, 140), (64, 200)]):
@@ -127,7 +127,7 @@ def test_dispersion_gain_against_direct_window_sums():
 
 def test_extended_gain_against_direct_window_sums():
     """DispersionExtendedThreshold::threshold_w_gain restatement (baseline.cpp:484-541, 657-714,
-    772-805; parity unpinned) vs direct integer window sums and the same fp64 formulas in numpy:
+    772-805; pinned in tests/test_oracle_refext.py) vs direct integer window sums and the same fp64 formulas in numpy:
     first pass on the 7x7 window of mask-valid pixels, final pass on the 11x11 window of the
     pixels the (gain-independent) erosion left valid."""
     from ffs_b200 import synth
