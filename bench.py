@@ -106,22 +106,27 @@ def workload_config(cfg, name, batch, n_distinct):
 # CPU arm: the reference's own CPU implementation of the path
 # ---------------------------------------------------------------------------------------------
 class CpuPath:
-    """threshold: the reference's standalone.cc compiled in place (oracle/_ref) for standard
-    dispersion, the oracle port for dispersion_extended (baseline.cpp needs DIALS headers);
-    connected components + filters: the oracle port (Boost.Graph CC is not buildable here);
-    chunk decode (from_chunks): the oracle's scalar bitshuffle-LZ4 port."""
+    """The reference's own CPU code for every step it has some, compiled in place under oracle/_ref
+    (oracle/Makefile): threshold = standalone.cc (standard dispersion) or baseline.cpp's
+    DispersionExtendedThreshold (dispersion_extended); connected components + both filters =
+    connected_components.cc (ConnectedComponents + find_2d_components, one object per frame as
+    spotfinder.cc:897-926 builds them).  Where a library is not built the oracle port stands in
+    and `kind` says "port".  Chunk decode (from_chunks): the oracle's scalar bitshuffle-LZ4 port
+    (the reference links the bitshuffle library, which is not in the image)."""
 
     def __init__(self, mask, n_threads, algorithm="dispersion"):
         from oracle import oracle
         self.o = oracle
         self.mask = np.ascontiguousarray(mask, np.uint8)
         self.algorithm = algorithm
-        self.kind = "reference" if (algorithm == "dispersion" and oracle.ref_available()) else "port"
         self.n_threads = n_threads
         self.h, self.w = mask.shape
         self.local = threading.local()
         self.L = oracle.lib()
-        self.R = oracle.ref() if self.kind == "reference" else None
+        self.R = oracle.ref() if (algorithm == "dispersion" and oracle.ref_available()) else None
+        self.X = oracle.refext() if (algorithm != "dispersion" and oracle.refext_available()) else None
+        self.cc_ok = oracle.refcc_available(2) and oracle.refcc_available(4)
+        self.kind = "reference" if ((self.R or self.X) and self.cc_ok) else "port"
         # ONE pool for the object's lifetime: a reference context is ~0.6 GB at 16M and lives in
         # its worker thread, so a pool per run() would leak n_threads contexts per step.
         self.ex = ThreadPoolExecutor(max_workers=n_threads)
@@ -129,14 +134,25 @@ class CpuPath:
         self.lock = threading.Lock()
 
     def describe(self):
-        thr = ("reference standalone.cc compiled in place (oracle/_ref)" if self.kind == "reference"
-               else "oracle port (baseline.cpp restated)")
-        return f"threshold = {thr}, CC + filters = oracle port"
+        thr = ("reference standalone.cc compiled in place (oracle/_ref)" if self.R
+               else "reference baseline.cpp DispersionExtendedThreshold compiled in place (oracle/_ref)" if self.X
+               else "oracle port")
+        cc = ("reference connected_components.cc compiled in place (oracle/_ref; stand-in Boost.Graph)" if self.cc_ok
+              else "oracle port")
+        return f"threshold = {thr}, CC + filters = {cc}"
 
     def _ctx(self):
         if not hasattr(self.local, "ctx"):
             self.local.dst = np.empty((self.h, self.w), np.uint8)
-            self.local.ctx = self.R.ffs_ref_create(self.w, self.h) if self.R else None
+            self.local.spots = np.zeros(1 << 16, self.o.REFCC_SPOT_DTYPE)
+            if self.R:
+                self.local.ctx = self.R.ffs_ref_create(self.w, self.h)
+            elif self.X:
+                p = self.o.default_params()
+                self.local.ctx = self.X.ffs_refext_create(1, self.w, self.h, self.mask.ctypes.data, p.kernel_half_x,
+                                                          p.kernel_half_y, p.nsig_b, p.nsig_s, p.threshold, p.min_count)
+            else:
+                self.local.ctx = None
             if self.local.ctx:
                 with self.lock:
                     self.ctxs.append(self.local.ctx)
@@ -145,7 +161,10 @@ class CpuPath:
     def close(self):
         self.ex.shutdown(wait=True)
         for c in self.ctxs:
-            self.R.ffs_ref_free(c)
+            if self.R:
+                self.R.ffs_ref_free(c)
+            else:
+                self.X.ffs_refext_destroy(c)
         self.ctxs = []
 
     def one(self, frame):
@@ -156,12 +175,23 @@ class CpuPath:
         if self.R:
             self.R.ffs_ref_standard_dispersion(ctx, frame.ctypes.data, frame.dtype.itemsize,
                                                self.mask.ctypes.data, dst.ctypes.data)
+        elif self.X:
+            self.X.ffs_refext_run(ctx, frame.ctypes.data, frame.dtype.itemsize, dst.ctypes.data)
         else:
             p = self.o.default_params()
             fn = (self.L.ffs_oracle_dispersion if self.algorithm == "dispersion"
                   else self.L.ffs_oracle_dispersion_extended)
             fn(frame.ctypes.data, frame.dtype.itemsize, self.mask.ctypes.data, self.w, self.h, C.byref(p),
                dst.ctypes.data)
+        if self.cc_ok:
+            G = self.o.refcc(frame.dtype.itemsize)
+            h = G.ffs_refcc_new()
+            try:
+                G.ffs_refcc_add_slice(h, dst.ctypes.data, frame.ctypes.data, self.w, self.h, 3, None, None, None)
+                n = G.ffs_refcc_find_2d(h, 0, 3, 2.0, self.local.spots.ctypes.data, len(self.local.spots), None)
+            finally:
+                G.ffs_refcc_free(h)
+            return int(n)
         _, spots = self.o.connected_components(dst, frame, row_wrap=True, want_labels=False)
         kept, _, _ = self.o.filter_spots(spots, 3, 2.0)
         return len(kept)
@@ -169,7 +199,7 @@ class CpuPath:
     def run(self, frames, n_frames):
         """Process n_frames (cycled) frame-parallel over n_threads; returns seconds."""
         ex = self.ex
-        if len(self.ctxs) < self.n_threads and self.R:  # first call: let every worker build its context
+        if len(self.ctxs) < self.n_threads and (self.R or self.X):  # first call: let every worker build its context
             list(ex.map(self.one, [frames[i % len(frames)] for i in range(self.n_threads)]))
         t0 = time.perf_counter()
         list(ex.map(self.one, [frames[i % len(frames)] for i in range(n_frames)]))

@@ -198,11 +198,7 @@ def refext_available() -> bool:
     return (_HERE / "_ref/libffs_refext.so").exists()
 
 
-def refext_threshold(image, mask, algorithm=ALGO_DISPERSION_EXTENDED, params=None, gain=None, stage=3) -> np.ndarray:
-    """The reference's own CPU DispersionThreshold / DispersionExtendedThreshold (baseline/spotfinder/
-    baseline.cpp:259-310,730-805), compiled in place behind oracle/refext_shim.cc (stand-in scitbx /
-    DIALS headers: oracle/stub_dials).  stage 1 / 2 stop the extended algorithm after its first pass /
-    after the erosion.  Returns the (H, W) u8 plane."""
+def refext() -> C.CDLL:
     global _REFEXT
     if _REFEXT is None:
         _REFEXT = C.CDLL(str(_HERE / "_ref/libffs_refext.so"))
@@ -210,11 +206,26 @@ def refext_threshold(image, mask, algorithm=ALGO_DISPERSION_EXTENDED, params=Non
         _REFEXT.ffs_refext_threshold.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                                  C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_int,
                                                  C.c_void_p]
+        _REFEXT.ffs_refext_create.restype = C.c_void_p
+        _REFEXT.ffs_refext_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_double,
+                                              C.c_double, C.c_double, C.c_int]
+        _REFEXT.ffs_refext_destroy.argtypes = [C.c_void_p]
+        _REFEXT.ffs_refext_run.restype = C.c_long
+        _REFEXT.ffs_refext_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    return _REFEXT
+
+
+def refext_threshold(image, mask, algorithm=ALGO_DISPERSION_EXTENDED, params=None, gain=None, stage=3) -> np.ndarray:
+    """The reference's own CPU DispersionThreshold / DispersionExtendedThreshold (baseline/spotfinder/
+    baseline.cpp:259-310,730-805), compiled in place behind oracle/refext_shim.cc (stand-in scitbx /
+    DIALS headers: oracle/stub_dials).  stage 1 / 2 stop the extended algorithm after its first pass /
+    after the erosion.  Returns the (H, W) u8 plane."""
+    G = refext()
     image, mask, w, h, bpp = _prep(image, mask)
     p = params or default_params()
     g = None if gain is None else np.ascontiguousarray(gain, dtype=np.float64)
     out = np.zeros((h, w), np.uint8)
-    n = _REFEXT.ffs_refext_threshold(algorithm, image.ctypes.data, bpp, mask.ctypes.data, w, h, p.kernel_half_x, p.kernel_half_y,
+    n = G.ffs_refext_threshold(algorithm, image.ctypes.data, bpp, mask.ctypes.data, w, h, p.kernel_half_x, p.kernel_half_y,
                                      p.nsig_b, p.nsig_s, p.threshold, p.min_count,
                                      None if g is None else g.ctypes.data, stage, out.ctypes.data)
     if n < 0:

@@ -89,4 +89,61 @@ long ffs_refext_threshold(int algorithm, const void* image, int bytes_per_pixel,
     }
 }
 
+// Persistent context for timing runs (bench.py --impl reference): buffers and the algorithm object
+// are built once, as the reference's own _spotfind_context does (baseline.cpp:817-842); a call
+// converts the pixels to double and runs threshold(), like spotfinder_standard_dispersion (:858-878).
+struct refext_ctx {
+    int algorithm, width, height;
+    std::vector<double> src;
+    std::unique_ptr<bool[]> mask, dst;
+    std::unique_ptr<baseline::DispersionThreshold> disp;
+    std::unique_ptr<baseline::DispersionExtendedThreshold> ext;
+};
+
+void* ffs_refext_create(int algorithm, int width, int height, const uint8_t* mask_u8, int kernel_half_x, int kernel_half_y,
+                        double nsig_b, double nsig_s, double threshold, int min_count) {
+    try {
+        auto c = std::make_unique<refext_ctx>();
+        const size_t n = (size_t)width * height;
+        c->algorithm = algorithm, c->width = width, c->height = height;
+        c->src.resize(n);
+        c->mask.reset(new bool[n]);
+        c->dst.reset(new bool[n]);
+        for (size_t k = 0; k < n; ++k) c->mask[k] = mask_u8[k] != 0;
+        const af::tiny<int, 2> size(height, width), kernel(kernel_half_y, kernel_half_x);
+        if (algorithm == 0) c->disp = std::make_unique<baseline::DispersionThreshold>(size, kernel, nsig_b, nsig_s, threshold, min_count);
+        else c->ext = std::make_unique<baseline::DispersionExtendedThreshold>(size, kernel, nsig_b, nsig_s, threshold, min_count);
+        return c.release();
+    } catch (const std::exception&) {
+        return nullptr;
+    }
+}
+
+void ffs_refext_destroy(void* ctx) { delete static_cast<refext_ctx*>(ctx); }
+
+long ffs_refext_run(void* ctx, const void* image, int bytes_per_pixel, uint8_t* out) {
+    auto* c = static_cast<refext_ctx*>(ctx);
+    try {
+        const size_t n = (size_t)c->width * c->height;
+        if (bytes_per_pixel == 2)
+            for (size_t k = 0; k < n; ++k) c->src[k] = static_cast<const uint16_t*>(image)[k];
+        else
+            for (size_t k = 0; k < n; ++k) c->src[k] = static_cast<const uint32_t*>(image)[k];
+        const af::c_grid<2> grid(c->height, c->width);
+        af::const_ref<double, af::c_grid<2>> s(c->src.data(), grid);
+        af::const_ref<bool, af::c_grid<2>> m(c->mask.get(), grid);
+        af::ref<bool, af::c_grid<2>> d(c->dst.get(), grid);
+        if (c->disp) c->disp->threshold(s, m, d);
+        else c->ext->threshold(s, m, d);
+        long count = 0;
+        for (size_t k = 0; k < n; ++k) {
+            out[k] = c->dst[k] ? 1 : 0;
+            count += out[k];
+        }
+        return count;
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
+
 }  // extern "C"
