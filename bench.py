@@ -241,12 +241,20 @@ def run_reference_arm(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    if args.config == "sweep3600":  # + 3D connected components of the sampled frames (oracle port)
+    if args.config == "sweep3600":  # + 3D connected components of the sampled frames, single thread
         from oracle import oracle
         strong = np.stack([oracle.dispersion(f, mask) for f in frames])
-        t0 = time.perf_counter()
-        oracle.connected_components(strong, frames, want_labels=False)
-        t3 = (time.perf_counter() - t0) / len(frames)
+        if oracle.refcc_available(frames.dtype.itemsize):  # the reference's own find_3d_components
+            with oracle.RefCC(frames, strong, 3) as r:
+                t0 = time.perf_counter()
+                r.find_3d(3, 2.0)
+                t3 = (time.perf_counter() - t0) / len(frames)
+            out["cpu_baseline"]["cc3d_code"] = "reference find_3d_components (oracle/_ref/libffs_refcc)"
+        else:
+            t0 = time.perf_counter()
+            oracle.connected_components(strong, frames, want_labels=False)
+            t3 = (time.perf_counter() - t0) / len(frames)
+            out["cpu_baseline"]["cc3d_code"] = "oracle port"
         out["cpu_baseline"]["cc3d_s_per_frame_single_thread"] = t3
         out["value"] = out["e2e"]["value"] = out["cpu_baseline"]["value"] = 1.0 / (1.0 / fps + t3)
     if not args.no_chunks:  # the real loop starts from the compressed chunk (spotfinder.cc:807-834)
