@@ -339,7 +339,10 @@ class Object {
     inline std::vector<Filter> filters() const;
     inline uint64_t n_elements() const {
         uint64_t n = 1;
-        for (uint64_t d : shape()) n *= d;
+        for (uint64_t d : shape()) {
+            if (d != 0 && n > (~0ull) / d) throw Error("h5lite: dataset extent overflows");
+            n *= d;
+        }
         return n;
     }
     // Where the chunk whose first element is at `offset` (element coordinates) is stored.
@@ -434,15 +437,14 @@ class File {
 
     // Bounds-checked view of n bytes at file address `addr` (relative to the base address).
     const uint8_t* at(uint64_t addr, uint64_t n) const {
-        const uint64_t a = addr + base_;
-        if (addr == UNDEF || a > map_len_ || n > map_len_ - a)
+        // (addr + base_ must not wrap: a damaged file can hold any 64-bit value here)
+        if (addr > map_len_ || base_ > map_len_ - addr || n > map_len_ - (addr + base_))
             throw Error("h5lite: " + path_ + ": address " + std::to_string(addr) + " + " + std::to_string(n) +
                         " is outside the file");
-        return map_ + a;
+        return map_ + (addr + base_);
     }
     bool in_file(uint64_t addr, uint64_t n) const {
-        const uint64_t a = addr + base_;
-        return addr != UNDEF && a <= map_len_ && n <= map_len_ - a;
+        return addr <= map_len_ && base_ <= map_len_ - addr && n <= map_len_ - (addr + base_);
     }
 
     inline Object object_at(uint64_t addr) const;
@@ -1268,9 +1270,12 @@ inline std::vector<uint8_t> Object::read_raw() const {
     const Datatype dt = dtype();
     const auto dims = shape();
     uint64_t n = 1;
-    for (uint64_t d : dims) n *= d;
+    for (uint64_t d : dims) {  // the product must not wrap: a damaged file can hold any extent
+        if (d != 0 && n > (1ull << 36) / d) throw Error("h5lite: dataset too large to read whole");
+        n *= d;
+    }
+    if (dt.size != 0 && n > (1ull << 36) / dt.size) throw Error("h5lite: dataset too large to read whole");
     const uint64_t bytes = n * dt.size;
-    if (bytes > (1ull << 36)) throw Error("h5lite: dataset too large to read whole");
     std::vector<uint8_t> out(bytes, 0);
     if (l.cls == Layout::Compact) {
         memcpy(out.data(), l.compact.data(), std::min<uint64_t>(bytes, l.compact.size()));
@@ -1281,10 +1286,13 @@ inline std::vector<uint8_t> Object::read_raw() const {
         const size_t rank = dims.size();
         if (rank == 0 || l.chunk.size() != rank) throw Error("h5lite: chunk rank");
         std::vector<uint64_t> nch(rank), off(rank, 0);
-        uint64_t total = 1;
+        uint64_t total = 1, chunk_elems = 1;
         for (size_t d = 0; d < rank; ++d) {
+            if (l.chunk[d] == 0) throw Error("h5lite: zero chunk dimension");
             nch[d] = (dims[d] + l.chunk[d] - 1) / l.chunk[d];
-            total *= nch[d];
+            total *= nch[d];  // <= n, checked above
+            if (chunk_elems > (1ull << 36) / l.chunk[d]) throw Error("h5lite: chunk too large");
+            chunk_elems *= l.chunk[d];
         }
         // row length that is contiguous in both the chunk and the dataset: the last dimension
         for (uint64_t ci = 0; ci < total; ++ci) {
@@ -1295,9 +1303,9 @@ inline std::vector<uint8_t> Object::read_raw() const {
             }
             const ChunkInfo c = find_chunk(off);
             if (!c.found) continue;
-            uint64_t cbytes = dt.size;
-            for (uint64_t cd : l.chunk) cbytes *= cd;
-            const uint8_t* src = f_->at(c.addr, std::min<uint64_t>(c.size, cbytes));
+            const uint64_t cbytes = chunk_elems * dt.size;
+            if (c.size < cbytes) throw Error("h5lite: stored chunk is smaller than its extent");
+            const uint8_t* src = f_->at(c.addr, cbytes);
             // walk the rows of the chunk (all dimensions but the last)
             uint64_t rows = 1;
             for (size_t d = 0; d + 1 < rank; ++d) rows *= l.chunk[d];
