@@ -237,3 +237,43 @@ def test_sample_source(exe, dtype, tmp_path):
     # the file group is required unless the environment says otherwise (spotfinder.cc:266-282)
     rc, _, out, _ = run(exe, [])
     assert rc == 1 and "One of the arguments '--sample' or 'FILE.nxs' is required" in out
+
+
+def test_data_file_that_arrives_late(tmp_path):
+    """The master (VDS) is there, the second data file is not: the frame loop polls
+    is_image_available (spotfinder.cc:770-787) and carries on when the file lands, like a reader
+    following a writer; a file that never comes ends the run with the timeout message, exit 0."""
+    import threading
+    import time
+    g = synth.small_geometry(300, 200)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 6, np.uint16, config=8, n_spots=10)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 16)
+    nxs = to_nxs(sd, tmp_path / "scan", per_file=3)
+    late = tmp_path / "scan_000002.h5"
+    parked = tmp_path / "parked.h5"
+    late.rename(parked)
+
+    def deliver():
+        time.sleep(1.5)
+        half = parked.read_bytes()
+        late.write_bytes(half[:len(half) // 3])      # first a truncated file (index not there yet) ...
+        time.sleep(0.5)
+        late.write_bytes(half)                        # ... then all of it
+    t = threading.Thread(target=deliver)
+    t.start()
+    rc, lines, out, err = run("spotfinder", [nxs, "--threads", "2", "--timeout", "20"])
+    t.join()
+    assert rc == 0, out + err
+    assert sorted(l["file-number"] for l in lines) == list(range(6))
+    want = expected_stills(frames, mask)
+    assert {l["file-number"]: l["num_strong_pixels"] for l in lines} == {i: want[i][0] for i in range(6)}
+    waited = float(re.search(r"Total time waiting for images to appear: ([0-9.]+) (ms|s)", out).group(1))
+    assert waited > 0
+
+    late.unlink()
+    rc, lines, out, err = run("spotfinder", [nxs, "--threads", "2", "--timeout", "1"])
+    assert rc == 0 and "Timeout waiting for image 3" in out
+    assert sorted(l["file-number"] for l in lines) == [0, 1, 2]
