@@ -318,6 +318,10 @@ static int cmd_stream2nxs(const std::string& dir, const std::string& prefix, siz
             w.dataset(det, "saturation_value", Datatype::u16(), {}, &v);
         }
     }
+    {   // NXmx underload_value: counts below it are invalid (h5read.c:809-816 reads it, default 0)
+        const int32_t under = 0;
+        w.dataset(det, "underload_value", Datatype::i32(), {}, &under);
+    }
     {   // start_5: int32 mask, non-zero = masked -> NXmx pixel_mask (uint32, non-zero = masked)
         const auto m = slurp(dir + "/start_5");
         if (m.size() != H * W * 4) throw Error("start_5 has the wrong size");

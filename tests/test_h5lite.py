@@ -470,8 +470,8 @@ def test_h5read_metadata_and_chunks(tmp_path, mode):
     frames, mask = make_scan(tmp_path, mode=mode)
     info, out, err = h5read(tmp_path / "scan.nxs")
     assert info["frames"] == 7 and info["shape"] == [64, 96] and info["element_size"] == 2
-    assert info["trusted"] == [0, 60000]                      # saturation_value; no underload_value (h5read.c:793-817)
-    assert "Warning: No underload_value found, using 0" in err
+    assert info["trusted"] == [0, 60000]                      # underload_value, saturation_value (h5read.c:793-817)
+    assert err == ""                                          # a complete NXmx file draws no warnings
     assert info["mask_valid"] == int(mask.sum())              # valid = (pixel_mask == 0) (h5read.c:615-633)
     assert "mask dtype uint32" in out and f"Mask has {mask.size} elements" in out and "Total data size: 7x64x96" in out
     assert info["wavelength"] == pytest.approx(0.976) and info["distance"] == pytest.approx(0.15)
