@@ -21,7 +21,8 @@
 // fixed, float, string, variable-length string, enum datatypes; layout 3 and 4: compact,
 // contiguous, chunked (version 1 B-tree, single chunk, implicit, fixed array, extensible
 // array), virtual (VDS mapping list with regular hyperslabs); filter pipeline 1/2; attribute
-// 1/2/3; global heap.  No filters are applied here: filtered chunks are handed out raw, which
+// 1/2/3; global heap; the lookup3 checksums of the version 2 structures are verified (a mismatch
+// reads as "not there yet" to the SWMR-style polling of reader_h5.hpp).  No filters are applied here: filtered chunks are handed out raw, which
 // is what the frame loop wants (the decode runs on the device).
 #pragma once
 #include <fcntl.h>
@@ -61,6 +62,42 @@ inline unsigned log2_floor(uint64_t v) {
     unsigned r = 0;
     while (v >>= 1) ++r;
     return r;
+}
+
+// The metadata checksum of the version 2 structures: Bob Jenkins' lookup3 `hashlittle` (public
+// domain algorithm), bytes taken little-endian, initial value 0.  Pinned by the three version 2
+// object headers of the reference's cut_strong.refl, whose stored checksums it reproduces.
+inline uint32_t lookup3(const uint8_t* k, size_t length, uint32_t initval = 0) {
+    auto rot = [](uint32_t x, int r) { return (x << r) | (x >> (32 - r)); };
+    uint32_t a, b, c;
+    a = b = c = 0xdeadbeefu + (uint32_t)length + initval;
+    auto word = [&](const uint8_t* p, size_t n) {  // up to 4 bytes, little-endian, zero-extended
+        uint32_t v = 0;
+        for (size_t i = 0; i < n && i < 4; ++i) v |= (uint32_t)p[i] << (8 * i);
+        return v;
+    };
+    while (length > 12) {
+        a += word(k, 4), b += word(k + 4, 4), c += word(k + 8, 4);
+        a -= c, a ^= rot(c, 4), c += b;
+        b -= a, b ^= rot(a, 6), a += c;
+        c -= b, c ^= rot(b, 8), b += a;
+        a -= c, a ^= rot(c, 16), c += b;
+        b -= a, b ^= rot(a, 19), a += c;
+        c -= b, c ^= rot(b, 4), b += a;
+        length -= 12, k += 12;
+    }
+    if (length == 0) return c;
+    a += word(k, length);
+    if (length > 4) b += word(k + 4, length - 4);
+    if (length > 8) c += word(k + 8, length - 8);
+    c ^= b, c -= rot(b, 14);
+    a ^= c, a -= rot(c, 11);
+    b ^= a, b -= rot(a, 25);
+    c ^= b, c -= rot(b, 16);
+    a ^= c, a -= rot(c, 4);
+    b ^= a, b -= rot(a, 14);
+    c ^= b, c -= rot(b, 24);
+    return c;
 }
 }  // namespace detail
 
@@ -400,6 +437,8 @@ class File {
             base_ = rd_le(at(off + 12, 8), 8);
             eof_ = rd_le(at(off + 28, 8), 8);
             root_addr_ = rd_le(at(off + 36, 8), 8);
+            if (detail::lookup3(map_ + off, 44) != (uint32_t)rd_le(at(off + 44, 4), 4))
+                throw Error("h5lite: " + path_ + ": superblock checksum mismatch");
         } else {
             throw Error("h5lite: superblock version " + std::to_string(version_) + " not handled");
         }
@@ -442,6 +481,15 @@ class File {
             throw Error("h5lite: " + path_ + ": address " + std::to_string(addr) + " + " + std::to_string(n) +
                         " is outside the file");
         return map_ + (addr + base_);
+    }
+    // Checks the 4-byte checksum stored right behind the n bytes at addr.  A mismatch is what a
+    // reader sees when it catches a SWMR writer half way through a block: callers treat the
+    // Error as "not there yet" and look again.
+    void verify(uint64_t addr, uint64_t n, const char* what) const {
+        const uint8_t* p = at(addr, n + 4);
+        if (detail::lookup3(p, n) != (uint32_t)rd_le(p + n, 4))
+            throw Error(std::string("h5lite: ") + path_ + ": checksum mismatch in " + what + " at " + std::to_string(addr) +
+                        " (damaged, or being written)");
     }
     bool in_file(uint64_t addr, uint64_t n) const {
         return addr <= map_len_ && base_ <= map_len_ - addr && n <= map_len_ - (addr + base_);
@@ -490,6 +538,7 @@ inline Object File::object_at(uint64_t addr) const {
         const uint64_t chunk0 = rd_le(at(p, szlen), szlen);
         p += szlen;
         const bool track = flags & 4;
+        verify(addr, p + chunk0 - addr, "an object header");
         blocks.push_back({p, chunk0});
         for (size_t bi = 0; bi < blocks.size() && bi < 4096; ++bi) {
             uint64_t q = blocks[bi].addr;
@@ -508,6 +557,7 @@ inline Object File::object_at(uint64_t addr) const {
                     if (size < 16) throw Error("h5lite: continuation message");
                     const uint64_t ca = rd_le(d, 8), cl = rd_le(d + 8, 8);
                     if (cl < 8 || memcmp(at(ca, 4), "OCHK", 4) != 0) throw Error("h5lite: continuation block");
+                    verify(ca, cl - 4, "an object header continuation");
                     blocks.push_back({ca + 4, cl - 8});  // without signature and checksum
                 } else if (type != 0) {
                     o.msgs_.push_back({type, mflags, std::vector<uint8_t>(d, d + size)});
@@ -736,6 +786,7 @@ template <class F>
 inline void btree_v2_records(const File& f, uint64_t addr, F&& visit) {
     const uint8_t* h = f.at(addr, 34);
     if (memcmp(h, "BTHD", 4) != 0 || h[4] != 0) throw Error("h5lite: version 2 B-tree header");
+    f.verify(addr, 34, "a version 2 B-tree header");
     const uint64_t node_size = rd_le(h + 6, 4), rec = rd_le(h + 10, 2);
     const unsigned depth = (unsigned)rd_le(h + 12, 2);
     const uint64_t root = rd_le(h + 16, 8);
@@ -763,9 +814,10 @@ inline void btree_v2_records(const File& f, uint64_t addr, F&& visit) {
         void node(uint64_t a, unsigned nrec, unsigned d) {
             const uint8_t* n = f.at(a, 6 + (uint64_t)nrec * rec);
             if (memcmp(n, d ? "BTIN" : "BTLF", 4) != 0) throw Error("h5lite: version 2 B-tree node signature");
+            const uint64_t ptr = 8 + nrec_size + (d > 1 ? cum_size[d - 1] : 0);
+            f.verify(a, 6 + (uint64_t)nrec * rec + (d ? (nrec + 1) * ptr : 0), "a version 2 B-tree node");
             for (unsigned i = 0; i < nrec; ++i) visit(n + 6 + i * rec);
             if (!d) return;
-            const uint64_t ptr = 8 + nrec_size + (d > 1 ? cum_size[d - 1] : 0);
             const uint64_t p0 = a + 6 + (uint64_t)nrec * rec;
             for (unsigned i = 0; i <= nrec; ++i) {
                 const uint8_t* p = f.at(p0 + i * ptr, ptr);
@@ -1155,6 +1207,7 @@ inline ChunkInfo fixed_array_chunk(const File& f, uint64_t addr, uint64_t idx, u
     if (addr == UNDEF) return none;
     const uint8_t* h = f.at(addr, 28);
     if (memcmp(h, "FAHD", 4) != 0) throw Error("h5lite: fixed array header signature");
+    f.verify(addr, 24, "a fixed array header");
     const bool filtered = h[5] == 1;
     const unsigned entry = h[6], page_bits = h[7];
     const uint64_t nelmts = rd_le(h + 8, 8), dblk = rd_le(h + 16, 8);
@@ -1166,11 +1219,16 @@ inline ChunkInfo fixed_array_chunk(const File& f, uint64_t addr, uint64_t idx, u
         const uint64_t npages = (nelmts + page_n - 1) / page_n;
         const uint64_t bitmap = (npages + 7) / 8;
         const uint64_t page = idx / page_n;
+        f.verify(dblk, 14 + bitmap, "a fixed array data block");
         const uint8_t* bm = f.at(p, bitmap);
         if (!(bm[page / 8] & (0x80 >> (page % 8)))) return none;  // page never written
         p += bitmap + 4;
-        p += page * (page_n * entry + 4) + (idx % page_n) * entry;
+        const uint64_t page_addr = p + page * (page_n * entry + 4);
+        const uint64_t in_page = std::min<uint64_t>(page_n, nelmts - page * page_n);  // the last page may be short
+        f.verify(page_addr, in_page * entry, "a fixed array page");
+        p = page_addr + (idx % page_n) * entry;
     } else {
+        f.verify(dblk, 14 + nelmts * entry, "a fixed array data block");
         p += idx * entry;
     }
     return decode_array_element(f.at(p, entry), entry, filtered, plain_size);
@@ -1182,6 +1240,7 @@ inline ChunkInfo ext_array_chunk(const File& f, uint64_t addr, uint64_t idx, uin
     if (addr == UNDEF) return none;
     const uint8_t* h = f.at(addr, 12 + 48 + 8);
     if (memcmp(h, "EAHD", 4) != 0) throw Error("h5lite: extensible array header signature");
+    f.verify(addr, 12 + 48 + 8, "an extensible array header");
     const bool filtered = h[5] == 1;
     const unsigned entry = h[6], max_bits = h[7], idx_elmts = h[8], dblk_min = h[9], sblk_min_ptrs = h[10],
                    page_bits = h[11];
@@ -1194,6 +1253,10 @@ inline ChunkInfo ext_array_chunk(const File& f, uint64_t addr, uint64_t idx, uin
     const unsigned ndblk_addrs = 2 * (sblk_min_ptrs - 1);
     const uint64_t page_n = 1ull << page_bits;
     if (memcmp(f.at(iblk, 4), "EAIB", 4) != 0) throw Error("h5lite: extensible array index block signature");
+    const unsigned nsblks_total = 1 + (max_bits - log2_floor(dblk_min));
+    const unsigned nsblk_addrs = nsblks_total > iblock_nsblks ? nsblks_total - iblock_nsblks : 0;
+    f.verify(iblk, 4 + 2 + 8 + (uint64_t)idx_elmts * entry + 8ull * ndblk_addrs + 8ull * nsblk_addrs,
+             "an extensible array index block");
     const uint64_t ib_elmts = iblk + 4 + 2 + 8;
     if (idx < idx_elmts) return decode_array_element(f.at(ib_elmts + idx * entry, entry), entry, filtered, plain_size);
     const uint64_t ib_dblks = ib_elmts + (uint64_t)idx_elmts * entry;
@@ -1220,13 +1283,21 @@ inline ChunkInfo ext_array_chunk(const File& f, uint64_t addr, uint64_t idx, uin
         if (memcmp(f.at(sblk_addr, 4), "EASB", 4) != 0) throw Error("h5lite: extensible array super block signature");
         uint64_t p = sblk_addr + 4 + 2 + 8 + off_size;
         if (dblk_n > page_n) p += ndblks * (((dblk_n / page_n) + 7) / 8);  // page-initialised bitmaps
+        f.verify(sblk_addr, p + 8 * ndblks - sblk_addr, "an extensible array super block");
         dblk_addr = rd_le(f.at(p + 8 * d_in_s, 8), 8);
     }
     if (dblk_addr == UNDEF) return none;
     if (memcmp(f.at(dblk_addr, 4), "EADB", 4) != 0) throw Error("h5lite: extensible array data block signature");
     uint64_t p = dblk_addr + 4 + 2 + 8 + off_size;
-    if (dblk_n > page_n) p += 4 + (e_in_d / page_n) * (page_n * entry + 4) + (e_in_d % page_n) * entry;
-    else p += e_in_d * entry;
+    if (dblk_n > page_n) {
+        f.verify(dblk_addr, p - dblk_addr, "an extensible array data block");
+        const uint64_t page_addr = p + 4 + (e_in_d / page_n) * (page_n * entry + 4);
+        f.verify(page_addr, page_n * entry, "an extensible array page");
+        p = page_addr + (e_in_d % page_n) * entry;
+    } else {
+        f.verify(dblk_addr, p - dblk_addr + dblk_n * entry, "an extensible array data block");
+        p += e_in_d * entry;
+    }
     return decode_array_element(f.at(p, entry), entry, filtered, plain_size);
 }
 }  // namespace detail

@@ -313,6 +313,35 @@ def test_hyperslab_selection_encodings():
     assert tool("selection", bad.hex(), check=False).returncode == 1
 
 
+CK = h5dissect.with_checksum   # block + its lookup3 checksum
+
+
+def test_lookup3_reproduces_libhdf5_checksums():
+    """The three version 2 object headers of cut_strong.refl carry checksums computed by libhdf5."""
+    buf = (GOLD / "cut_strong.refl").read_bytes()
+    seen = 0
+    for addr in (0x320, 0x65E, 0x563):
+        assert buf[addr:addr + 4] == b"OHDR" and buf[addr + 4] == 2
+        flags = buf[addr + 5]
+        p = addr + 6 + (16 if flags & 0x20 else 0) + (4 if flags & 0x10 else 0)
+        n = 1 << (flags & 3)
+        end = p + n + int.from_bytes(buf[p:p + n], "little")
+        assert h5dissect.lookup3(buf[addr:end]) == struct.unpack_from("<I", buf, end)[0]
+        seen += 1
+    assert seen == 3
+
+
+def test_cpp_reader_verifies_checksums(tmp_path):
+    """The C++ reader checks them while it walks the file: one flipped payload bit is noticed."""
+    bad = bytearray((GOLD / "cut_strong.refl").read_bytes())
+    bad[0x320 + 20] ^= 1
+    p = tmp_path / "bad.refl"
+    p.write_bytes(bad)
+    r = tool("dump", p, check=False)
+    assert r.returncode == 1 and b"checksum mismatch in an object header" in r.stderr
+    assert tool("dump", GOLD / "cut_strong.refl").returncode == 0
+
+
 def _patch_layout(buf, new_layout):
     """Replace the version 3 chunked layout message of the single dataset in `buf`."""
     # message header (type 8, size 32, flags 0) + version 3, chunked, dimensionality 4 (rank 3 + element size)
@@ -341,7 +370,7 @@ def test_fixed_array_chunk_index(tmp_path):
         nelmts, entry = N_STRESS, 8
         hdr_addr = len(buf)
         dblk_addr = hdr_addr + 28
-        hdr = b"FAHD" + bytes([0, 0, entry, page_bits]) + struct.pack("<QQ", nelmts, dblk_addr) + bytes(4)
+        hdr = CK(b"FAHD" + bytes([0, 0, entry, page_bits]) + struct.pack("<QQ", nelmts, dblk_addr))
         elems = [struct.pack("<Q", chunks[i][0] if i in chunks else h5dissect.UNDEF) for i in range(nelmts)]
         dblk = b"FADB" + bytes([0, 0]) + struct.pack("<Q", hdr_addr)
         page_n = 1 << page_bits
@@ -350,11 +379,11 @@ def test_fixed_array_chunk_index(tmp_path):
             bitmap = bytearray(-(-npages // 8))
             for p in range(npages):
                 bitmap[p // 8] |= 0x80 >> (p % 8)
-            dblk += bytes(bitmap) + bytes(4)
+            dblk = CK(dblk + bytes(bitmap))
             for p in range(npages):
-                dblk += b"".join(elems[p * page_n:(p + 1) * page_n]) + bytes(4)
+                dblk += CK(b"".join(elems[p * page_n:(p + 1) * page_n]))
         else:
-            dblk += b"".join(elems) + bytes(4)
+            dblk = CK(dblk + b"".join(elems))
         buf += hdr + dblk
         lay = bytes([4, 2, 0, 4, 4]) + struct.pack("<4I", 1, 4, 5, 2) + bytes([3, page_bits]) + struct.pack("<Q", hdr_addr)
         _patch_layout(buf, lay)
@@ -395,7 +424,7 @@ def test_extensible_array_chunk_index(tmp_path):
         addr = cursor
         body = b"EADB" + bytes([0, 0]) + struct.pack("<Q", hdr_addr) + struct.pack("<I", first - idx_elmts)
         body += b"".join(struct.pack("<Q", addr_of(i) if i < nelmts else h5dissect.UNDEF) for i in range(first, first + n))
-        body += bytes(4)
+        body = CK(body)
         blocks += body
         cursor += len(body)
         return addr
@@ -415,7 +444,7 @@ def test_extensible_array_chunk_index(tmp_path):
                 first += ne
             sb = cursor
             body = b"EASB" + bytes([0, 0]) + struct.pack("<Q", hdr_addr) + struct.pack("<I", 0)
-            body += b"".join(struct.pack("<Q", k) for k in kids) + bytes(4)
+            body = CK(body + b"".join(struct.pack("<Q", k) for k in kids))
             blocks += body
             cursor += len(body)
             sblk_addrs.append(sb)
@@ -425,10 +454,10 @@ def test_extensible_array_chunk_index(tmp_path):
     assert sblk_addrs[0] != h5dissect.UNDEF  # 300 elements reach the first super block outside the index block
 
     hdr = b"EAHD" + bytes([0, 0, entry, max_bits, idx_elmts, dmin, smin, page_bits])
-    hdr += struct.pack("<6Q", 0, 0, 0, 0, nelmts, nelmts) + struct.pack("<Q", iblk_addr) + bytes(4)
+    hdr = CK(hdr + struct.pack("<6Q", 0, 0, 0, 0, nelmts, nelmts) + struct.pack("<Q", iblk_addr))
     iblk = b"EAIB" + bytes([0, 0]) + struct.pack("<Q", hdr_addr)
     iblk += b"".join(struct.pack("<Q", addr_of(i)) for i in range(idx_elmts))
-    iblk += b"".join(struct.pack("<Q", a) for a in dblk_addrs) + b"".join(struct.pack("<Q", a) for a in sblk_addrs) + bytes(4)
+    iblk = CK(iblk + b"".join(struct.pack("<Q", a) for a in dblk_addrs) + b"".join(struct.pack("<Q", a) for a in sblk_addrs))
     assert len(hdr) == hdr_len and len(iblk) == iblk_len
     buf += hdr + iblk + blocks
     lay = bytes([4, 2, 0, 4, 2]) + struct.pack("<4H", 1, 4, 5, 2) + bytes([4, max_bits, idx_elmts, smin, dmin, page_bits])
@@ -619,22 +648,22 @@ def test_dense_link_storage(tmp_path, layout):
     rec = lambda n: bytes(4) + ids[n]
     nodes_addr = blocks_addr + len(layout_bytes)
     if layout == "root-direct":
-        leaf = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in names) + bytes(4)
+        leaf = CK(b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in names))
         nodes = leaf
         bt_root, root_nrec, depth = nodes_addr, 30, 0
     else:
         left, mid, right = names[:15], names[15], names[16:]
-        leaf1 = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in left) + bytes(4)
-        leaf2 = b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in right) + bytes(4)
+        leaf1 = CK(b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in left))
+        leaf2 = CK(b"BTLF" + bytes([0, 5]) + b"".join(rec(n) for n in right))
         a1, a2 = nodes_addr, nodes_addr + len(leaf1)
-        internal = b"BTIN" + bytes([0, 5]) + rec(mid) + struct.pack("<QB", a1, len(left)) + struct.pack("<QB", a2, len(right)) + bytes(4)
+        internal = CK(b"BTIN" + bytes([0, 5]) + rec(mid) + struct.pack("<QB", a1, len(left)) + struct.pack("<QB", a2, len(right)))
         nodes = leaf1 + leaf2 + internal
         bt_root, root_nrec, depth = a2 + len(leaf2), 1, 1
-    bt = b"BTHD" + bytes([0, 5]) + struct.pack("<IHHBB", 512, 11, depth, 100, 40) + struct.pack("<QHQ", bt_root, root_nrec, 30) + bytes(4)
+    bt = CK(b"BTHD" + bytes([0, 5]) + struct.pack("<IHHBB", 512, 11, depth, 100, 40) + struct.pack("<QHQ", bt_root, root_nrec, 30))
     # --- the group's object header (version 2): link info + group info
     linfo = bytes([0, 0]) + struct.pack("<QQ", heap_addr, bt_addr)
     body = bytes([2]) + struct.pack("<H", len(linfo)) + bytes([0]) + linfo + bytes([10]) + struct.pack("<H", 2) + bytes([1, 0, 0])
-    ohdr = b"OHDR" + bytes([2, 0, len(body)]) + body + bytes(4)
+    ohdr = CK(b"OHDR" + bytes([2, 0, len(body)]) + body)
     assert len(ohdr) <= 64 and len(heap) <= 160 and len(bt) <= 64
     buf += ohdr + bytes(64 - len(ohdr)) + heap + bytes(160 - len(heap)) + bt + bytes(64 - len(bt)) + layout_bytes + nodes
     # --- hang it where /links was
