@@ -281,9 +281,9 @@ class H5Read : public Reader {
     bool is_image_available(size_t index) override {
         size_t local = index;
         DataFile* d = file_for(local);
-        if (!d) {
+        if (!d) {  // beyond every data file: a usage error (--images / --start-index), h5read.c:383-386 exits too
             fprintf(stderr, "Error: Could not find data file for frame %zu\n", index);
-            return false;
+            exit(1);
         }
         return locate(*d, local).found;
     }

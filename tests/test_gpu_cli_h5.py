@@ -277,3 +277,15 @@ def test_data_file_that_arrives_late(tmp_path):
     rc, lines, out, err = run("spotfinder", [nxs, "--threads", "2", "--timeout", "1"])
     assert rc == 0 and "Timeout waiting for image 3" in out
     assert sorted(l["file-number"] for l in lines) == [0, 1, 2]
+
+
+def test_more_images_than_the_scan_holds(tmp_path):
+    g = synth.small_geometry(96, 64)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 3, np.uint16, config=8, n_spots=3)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 16)
+    nxs = to_nxs(sd, tmp_path / "scan")
+    rc, lines, out, err = run("spotfinder", [nxs, "--images", "5", "--threads", "1"])
+    assert rc == 1 and "Could not find data file for frame 3" in err      # h5read.c:383-386
