@@ -289,3 +289,22 @@ def test_more_images_than_the_scan_holds(tmp_path):
     nxs = to_nxs(sd, tmp_path / "scan")
     rc, lines, out, err = run("spotfinder", [nxs, "--images", "5", "--threads", "1"])
     assert rc == 1 and "Could not find data file for frame 3" in err      # h5read.c:383-386
+
+
+def test_validate_script_on_a_nexus_file(tmp_path):
+    """tests/validate_stream.py (the stand-in for --validate) on .nxs input: frames read through
+    h5lite_tool, decoded by the oracle's bitshuffle-LZ4 port, strong pixels compared per frame."""
+    import sys
+    from pathlib import Path
+    g = synth.small_geometry(180, 140)
+    mask = synth.make_mask(g)
+    frames = synth.make_frames(g, mask, 4, np.uint16, config=6, n_spots=10)
+    sd = tmp_path / "stream"
+    sd.mkdir()
+    write_stream(sd, frames, mask, 16)
+    nxs = to_nxs(sd, tmp_path / "scan", per_file=3)
+    script = Path(__file__).resolve().parent / "validate_stream.py"
+    for algo in ("dispersion", "dispersion_extended"):
+        r = subprocess.run([sys.executable, str(script), nxs, "--algorithm", algo], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert r.stdout.count("identical") == 4 and "validation passed" in r.stdout
