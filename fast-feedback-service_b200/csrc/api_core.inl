@@ -221,6 +221,8 @@ extern "C" void ffs_destroy(ffs_ctx* c) {
     cudaFree(c->d_gain);
     cudaFree(c->d_frames);
     cudaFree(c->d_zero);
+    cudaFree(c->d_check);
+    if (c->check_stream) cudaStreamDestroy(c->check_stream);
     cudaFree(c->d_ext1);
     cudaFree(c->d_ext2);
     cudaFree(c->d_cand);

@@ -238,6 +238,7 @@ extern "C" int ffs_wait(ffs_ctx* c, ffs_frame_result* result, ffs_spot* spots, s
             }
         }
     }
+    if (rc == FFS_OK && c->self_check) rc = self_check_slot(c, slot);
     if (rc == FFS_OK && c->sweep_on) rc = sweep_record(c, slot, s.frame_id, cnt[CNT_STRONG]);
     if (rc == FFS_OK && c->keep_pixels) {  // --writeout: the frame's strong-pixel list, before the slot is reused
         c->last_pixels.resize(cnt[CNT_STRONG]);

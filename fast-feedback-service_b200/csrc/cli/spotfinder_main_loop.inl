@@ -67,7 +67,20 @@
     const bool timing_report = args.threads == 1;
     if (timing_report)
         for (ffs_ctx* c : ctxs) ffs_frame_timing(c, 1);
-    if (args.validate) printf("Note: --validate needs the CPU baseline, which this GPU-only build does not contain; use tests/validate_stream.py\n");
+    // --validate (spotfinder.cc:1010-1052): the reference re-runs its CPU DIALS code per image.  No CPU
+    // implementation lives in this build; the second opinion is the device's exact per-pixel routine
+    // (ffs_self_check, csrc/api_selfcheck.inl).  tests/validate_stream.py is the check against the CPU oracle.
+    bool validating = false;
+    if (args.validate) {
+        validating = true;
+        for (ffs_ctx* c : ctxs)
+            if (ffs_self_check(c, 1) != FFS_OK) validating = false;
+        if (validating)
+            printf("Validation: every image is decided a second time by the exact per-pixel kernel (direct window sums, "
+                   "no pruning) and the strong pixels are compared\n");
+        else
+            printf("Note: --validate covers standard dispersion only; not validating\n");
+    }
     // --save-h5 on stills: kept centroids per image, keyed by image number (spotfinder.cc:706-721,928-932)
     std::map<int, std::vector<float>> reflection_centers_2d;
     std::unique_ptr<PipeHandler> pipe;
@@ -92,6 +105,7 @@
     std::atomic<int> workers_alive{(int)args.threads};
     std::atomic<bool> had_error{false};
     std::atomic<uint32_t> failed_images{0};
+    std::atomic<uint32_t> validation_failures{0};
     std::vector<int> thread_of(num_images, 0);
     std::mutex wait_mutex;
     double time_waiting_for_images = 0;
@@ -307,6 +321,22 @@
                     snprintf(name, sizeof name, "image_%05u.png", image_num);
                     if (!pngw::write_rgb(name, rgb.data(), width, height)) printf("Warning: could not write %s\n", name);
                 }
+            }
+            uint32_t exact_strong = 0, mismatch = 0;
+            if (validating && ffs_last_self_check(ctx, &exact_strong, &mismatch) == FFS_OK) {
+                // the reference prints this line instead of the per-image summary (spotfinder.cc:1036-1051)
+                if (mismatch == 0)
+                    printf("Thread %2d, Image %4u: Compared: \033[32mMatch %u px\033[0m\n", thread_of[image_num], image_num,
+                           r.num_strong_pixels);
+                else {
+                    printf("Thread %2d, Image %4u: Compared: \033[1;31mMismatch (%u px from kernel)\033[0m\n",
+                           thread_of[image_num], image_num, r.num_strong_pixels);
+                    validation_failures++;
+                    had_error = true;  // unlike the reference, a failed validation is not a clean exit
+                }
+                completed++;
+                collected[dev]++;
+                continue;
             }
             float t_copy = 0, t_kernel = 0, t_post = 0;
             if (timing_report && ffs_last_frame_timing(ctx, &t_copy, &t_kernel, &t_post) == FFS_OK) {

@@ -147,6 +147,11 @@ struct ffs_ctx {
     std::vector<uint64_t> sweep_sums;      // per 3D component: exact sum I, (2x+1)I, (2y+1)I, (2z+1)I
     bool frame_timing = false;             // ffs_frame_timing: per-frame copy / kernel / post-copy times
     float last_timing[3] = {0, 0, 0};      // of the last ffs_wait frame, ms
+    bool self_check = false;               // ffs_self_check: ffs_wait decides every frame a second time (api_selfcheck.inl)
+    uint8_t* d_check = nullptr;            // [bit-plane | strong count, candidate count (0), differing bits]
+    size_t check_bytes = 0;
+    cudaStream_t check_stream = nullptr;
+    uint32_t last_check[2] = {0, 0};       // {strong pixels of the exact pass, differing pixels} of the last ffs_wait frame
     bool keep_pixels = false;              // ffs_keep_pixel_lists
     bool keep_frame = false;
     std::vector<uint8_t> last_frame;       // dense pixels of the last ffs_wait frame (keep mode 2)

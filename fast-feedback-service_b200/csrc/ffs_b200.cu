@@ -103,6 +103,7 @@ static int sweep_record(ffs_ctx* c, int slot, uint64_t frame_id, uint32_t n_stro
 #include "api_core.inl"
 #include "api_ext.inl"
 #include "api_cc.inl"
+#include "api_selfcheck.inl"
 #include "api_stream.inl"
 #include "api_bslz4.inl"
 #include "api_sweep.inl"

@@ -137,6 +137,8 @@ SYMBOLS = {
                                   C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_sz)]),
     "ffs_set_gain": (_i, [_vp, _vp]),
     "ffs_keep_pixel_lists": (_i, [_vp, _i]),
+    "ffs_self_check": (_i, [_vp, _i]),
+    "ffs_last_self_check": (_i, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "ffs_frame_timing": (_i, [_vp, _i]),
     "ffs_last_frame_timing": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "ffs_last_pixel_list": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),

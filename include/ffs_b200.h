@@ -234,6 +234,16 @@ int ffs_decode_chunk_device(ffs_ctx *ctx, int slot, const void *chunk, size_t ch
  * ffs_wait on this context.  on = 2 also keeps the dense frame as the device saw it (after the
  * device decode, if any), for the diagnostic picture. */
 int ffs_keep_pixel_lists(ffs_ctx *ctx, int on);
+
+/* --validate (spotfinder.cc:1010-1052: the reference runs its CPU DIALS code on the frame a second
+ * time and compares the strong pixels).  This library contains no CPU implementation, so the second
+ * opinion is the device's own exact per-pixel routine: when switched on, ffs_wait decides every
+ * pixel of the frame again from direct window sums (no streaming sums, no bounds, no pruning) into
+ * a plane of its own and counts the pixels on which the two planes differ.  Standard dispersion
+ * only (like the reference's --validate); costs a few ms per 16M frame.  ffs_last_self_check
+ * reports the last ffs_wait frame: strong pixels found by the exact pass, differing pixels. */
+int ffs_self_check(ffs_ctx *ctx, int on);
+int ffs_last_self_check(ffs_ctx *ctx, uint32_t *n_strong_exact, uint32_t *n_mismatch);
 /* The per-image timing block the reference prints with --threads 1 (spotfinder.cc:1055-1076: Copy /
  * Kernel / Post Copy): while on, every streamed frame is bracketed by CUDA events (and replayed
  * without its graph); ffs_last_frame_timing returns the times of the last ffs_wait frame in ms:
