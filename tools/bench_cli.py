@@ -36,22 +36,30 @@ from ffs_b200 import bslz4_encode, synth  # noqa: E402
 BIN = ROOT / "fast-feedback-service_b200" / "ffs_b200"
 
 
-def run(exe, args):
+def run(exe, args, workdir):
+    """stdout and stderr go to files: the executable prints a few lines per image, which would fill a
+    pipe nobody drains while this side is still reading the JSON lines."""
     r, w = os.pipe()
     t0 = time.perf_counter()
-    proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=subprocess.PIPE,
-                            stderr=subprocess.PIPE)
-    os.close(w)
-    n_lines = 0
-    with os.fdopen(r) as f:
-        for _ in f:
-            n_lines += 1
-    out, err = proc.communicate(timeout=600)
+    with open(workdir / "stdout.txt", "wb") as fo, open(workdir / "stderr.txt", "wb") as fe:
+        proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=fo, stderr=fe)
+        os.close(w)
+        n_lines = 0
+        with os.fdopen(r) as f:
+            for _ in f:
+                n_lines += 1
+        try:
+            proc.wait(timeout=300)
+        except subprocess.TimeoutExpired:
+            proc.kill()
+            proc.wait()
     wall = time.perf_counter() - t0
-    m = re.search(r"(\d+) images in ([0-9.]+) s \(([0-9.]+) GBps\) \(([0-9.]+) fps\)", out.decode())
+    out = (workdir / "stdout.txt").read_text(errors="replace")
+    err = (workdir / "stderr.txt").read_text(errors="replace")
+    m = re.search(r"(\d+) images in ([0-9.]+) s \(([0-9.]+) GBps\) \(([0-9.]+) fps\)", out)
     return {"rc": proc.returncode, "json_lines": n_lines, "images": int(m.group(1)) if m else 0,
             "seconds": float(m.group(2)) if m else None, "fps": float(m.group(4)) if m else None,
-            "wall_seconds_with_startup": wall, "stderr": err.decode()[-300:]}
+            "wall_seconds_with_startup": wall, "stderr": err[-300:]}
 
 
 def main():
@@ -91,7 +99,7 @@ def main():
                           "distance": 150.0})
         for source, path in (("stream", str(sd)), ("nxs", str(base / "scan.nxs"))):
             for t in args.threads:
-                r = run("spotfinder", [path, "--threads", str(t), "--detector", det])
+                r = run("spotfinder", [path, "--threads", str(t), "--detector", det], base)
                 r.update(source=source, threads=t)
                 print(source, t, r["fps"], r["rc"], file=sys.stderr)
                 out["runs"].append(r)
