@@ -67,6 +67,7 @@ def main():
     ap.add_argument("--frames", type=int, default=512)
     ap.add_argument("--threads", type=int, nargs="+", default=[8, 16, 32])
     ap.add_argument("--geometry", default="eiger2_16m")
+    ap.add_argument("--sources", nargs="+", default=["stream", "nxs"], choices=["stream", "nxs"])
     args = ap.parse_args()
     g = synth.GEOMETRIES[args.geometry]
     mask = synth.make_mask(g)
@@ -91,13 +92,16 @@ def main():
             (sd / f"image_{k:06d}_2").write_bytes(c)
         for i in range(8, args.frames):
             os.link(sd / f"image_{i % 8:06d}_2", sd / f"image_{i:06d}_2")
-        t0 = time.perf_counter()
-        subprocess.run([str(BIN / "h5lite_tool"), "stream2nxs", str(sd), str(base / "scan"), "128"], check=True,
-                       capture_output=True)
-        out["stream2nxs_seconds"] = time.perf_counter() - t0
+        if "nxs" in args.sources:
+            t0 = time.perf_counter()
+            subprocess.run([str(BIN / "h5lite_tool"), "stream2nxs", str(sd), str(base / "scan"), "128"], check=True,
+                           capture_output=True)
+            out["stream2nxs_seconds"] = time.perf_counter() - t0
         det = json.dumps({"pixel_size_x": 0.075, "pixel_size_y": 0.075, "beam_center_x": 155.0, "beam_center_y": 163.0,
                           "distance": 150.0})
         for source, path in (("stream", str(sd)), ("nxs", str(base / "scan.nxs"))):
+            if source not in args.sources:
+                continue
             for t in args.threads:
                 r = run("spotfinder", [path, "--threads", str(t), "--detector", det], base)
                 r.update(source=source, threads=t)
