@@ -10,7 +10,7 @@ would run it.  Two sources of the same frames, both in /dev/shm:
 
 Reports the executable's own summary line (`N images in T s (G GBps) (F fps)`, spotfinder.cc:1312-1322)
 per source and thread count, one JSON object on stdout.  Synthetic Eiger2 16M u16 frames; N frames
-cycle over 8 distinct ones (hard links in the stream directory; the data files hold every frame).
+cycle over 8 distinct ones (one file per frame in the stream directory, the data files hold every frame).
 """
 import argparse
 import json
@@ -67,6 +67,9 @@ def main():
     ap.add_argument("--frames", type=int, default=512)
     ap.add_argument("--threads", type=int, nargs="+", default=[8, 16, 32])
     ap.add_argument("--geometry", default="eiger2_16m")
+    ap.add_argument("--links", action="store_true",
+                    help="stream directory: hard links to 8 files instead of one file per frame (less /dev/shm, but "
+                         "every reader thread then hammers the same 8 inodes)")
     ap.add_argument("--sources", nargs="+", default=["stream", "nxs"], choices=["stream", "nxs"])
     args = ap.parse_args()
     g = synth.GEOMETRIES[args.geometry]
@@ -91,7 +94,10 @@ def main():
         for k, c in enumerate(chunks):
             (sd / f"image_{k:06d}_2").write_bytes(c)
         for i in range(8, args.frames):
-            os.link(sd / f"image_{i % 8:06d}_2", sd / f"image_{i:06d}_2")
+            if args.links:
+                os.link(sd / f"image_{i % 8:06d}_2", sd / f"image_{i:06d}_2")
+            else:
+                (sd / f"image_{i:06d}_2").write_bytes(chunks[i % 8])
         if "nxs" in args.sources:
             t0 = time.perf_counter()
             subprocess.run([str(BIN / "h5lite_tool"), "stream2nxs", str(sd), str(base / "scan"), "128"], check=True,
