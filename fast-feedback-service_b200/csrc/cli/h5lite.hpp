@@ -495,6 +495,19 @@ class File {
         return addr <= map_len_ && base_ <= map_len_ - addr && n <= map_len_ - (addr + base_);
     }
 
+    // Bulk data (a frame's chunk) is better read than mapped: many threads touching fresh pages of
+    // one mapping serialise on the page-fault path.  Returns false on a short read (file still growing).
+    bool read_into(uint64_t addr, uint64_t n, void* dst) const {
+        if (!in_file(addr, n)) return false;
+        uint64_t done = 0;
+        while (done < n) {
+            const ssize_t r = ::pread(fd_, static_cast<uint8_t*>(dst) + done, n - done, (off_t)(addr + base_ + done));
+            if (r <= 0) return false;
+            done += (uint64_t)r;
+        }
+        return true;
+    }
+
     inline Object object_at(uint64_t addr) const;
     Object root() const { return object_at(root_addr_); }
     // Follows hard and soft links inside this file; throws Error when a component is missing

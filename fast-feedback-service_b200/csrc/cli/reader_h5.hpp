@@ -296,9 +296,7 @@ class H5Read : public Reader {
         if (!c.found || c.size == 0) return 0;
         if (c.size > capacity) return SIZE_MAX;
         std::shared_lock<std::shared_mutex> lk(mutex_);
-        if (!d->file->in_file(c.addr, c.size)) return 0;
-        memcpy(dst, d->file->at(c.addr, c.size), c.size);
-        return c.size;
+        return d->file->read_into(c.addr, c.size, dst) ? c.size : 0;
     }
     bool get_raw_chunk(size_t index, std::vector<uint8_t>& dst) override {
         size_t local = index;
@@ -308,9 +306,8 @@ class H5Read : public Reader {
         dst.clear();
         if (!c.found) return true;  // "zero length": the caller sleeps and retries
         std::shared_lock<std::shared_mutex> lk(mutex_);
-        if (!d->file->in_file(c.addr, c.size)) return true;
-        const uint8_t* p = d->file->at(c.addr, c.size);
-        dst.assign(p, p + c.size);
+        dst.resize(c.size);
+        if (!d->file->read_into(c.addr, c.size, dst.data())) dst.clear();
         return true;
     }
     bool read_pixels(size_t index, void* dst, size_t bytes) override {
@@ -321,9 +318,7 @@ class H5Read : public Reader {
         const h5lite::ChunkInfo c = locate(*d, local);
         if (!c.found || c.size < bytes) return false;
         std::shared_lock<std::shared_mutex> lk(mutex_);
-        if (!d->file->in_file(c.addr, bytes)) return false;
-        memcpy(dst, d->file->at(c.addr, bytes), bytes);
-        return true;
+        return d->file->read_into(c.addr, bytes, dst);
     }
 
     size_t get_number_of_images() const override { return frames_; }

@@ -116,6 +116,10 @@
     // developer knob (honoured only with FFS_DEV_KNOBS=1, like the library's): decode chunks on the host
     const bool host_decode = getenv("FFS_DEV_KNOBS") && atoi(getenv("FFS_DEV_KNOBS")) != 0 &&
                              getenv("FFS_HOST_DECODE") && atoi(getenv("FFS_HOST_DECODE")) != 0;
+    // developer knob: where the worker threads' time goes (summed over threads, printed at the end)
+    const bool cli_timing = getenv("FFS_DEV_KNOBS") && atoi(getenv("FFS_DEV_KNOBS")) != 0 && getenv("FFS_CLI_TIMING");
+    std::atomic<long long> ns_avail{0}, ns_acquire{0}, ns_read{0}, ns_submit{0};
+    auto ns_since = [](clk::time_point t) { return (long long)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t).count(); };
     auto worker = [&](int thread_id) {
         std::vector<uint8_t> chunk, scratch;
         while (!g_stop) {
@@ -139,10 +143,13 @@
                 std::lock_guard<std::mutex> lk(wait_mutex);
                 last_image_received = clk::now();
                 time_waiting_for_images += seconds_since(wait_start);
+                if (cli_timing) ns_avail += ns_since(wait_start);
             }
             int slot = -1;
             void* pinned = nullptr;
+            auto t_phase = clk::now();
             if (ffs_acquire(ctx, &slot, &pinned) != FFS_OK) break;
+            if (cli_timing) ns_acquire += ns_since(t_phase);
             thread_of[image_num] = thread_id;
             // The compressed chunk is read straight into the slot's pinned upload buffer, uploaded
             // and decoded on the device (bslz4_gpu.cuh).  The reference decompresses here on the
@@ -172,6 +179,7 @@
             const bool direct = !host_decode && ffs_slot_buffers(ctx, slot, nullptr, &pchunk, &cap) == FFS_OK;
             size_t chunk_bytes = 0;
             const uint8_t* chunk_data = nullptr;
+            t_phase = clk::now();
             for (;;) {  // zero-length chunk = writer not finished: sleep and retry (:805-821)
                 size_t got = direct ? reader.read_raw_chunk(offset_image_num, static_cast<uint8_t*>(pchunk), cap) : SIZE_MAX;
                 if (got == SIZE_MAX) {  // host path, or a chunk larger than the upload buffer
@@ -189,6 +197,8 @@
                 chunk_bytes = got;
                 break;
             }
+            if (cli_timing) ns_read += ns_since(t_phase);
+            t_phase = clk::now();
             int rc = FFS_ERR_FORMAT;
             if (chunk_bytes == 0) {  // stopped while waiting for the writer
                 ffs_release(ctx, slot);
@@ -211,6 +221,7 @@
                 had_error = true;
                 break;
             }
+            if (cli_timing) ns_submit += ns_since(t_phase);
             submitted[dev]++;
         }
         workers_alive--;
@@ -523,6 +534,9 @@
         printf("2D spot analysis complete\n");
     }
 
+    if (cli_timing)
+        printf("worker time, summed over threads (s): availability %.3f, slot acquire %.3f, chunk read %.3f, submit %.3f\n",
+               ns_avail * 1e-9, ns_acquire * 1e-9, ns_read * 1e-9, ns_submit * 1e-9);
     const double total_time = seconds_since(all_images_start);
     const uint32_t done = completed;
     printf("\n%u images in %.2f s (%.2f GBps) (%.1f fps)\n", done, total_time,

@@ -42,7 +42,8 @@ def run(exe, args, workdir):
     r, w = os.pipe()
     t0 = time.perf_counter()
     with open(workdir / "stdout.txt", "wb") as fo, open(workdir / "stderr.txt", "wb") as fe:
-        proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=fo, stderr=fe)
+        proc = subprocess.Popen([str(BIN / exe), *args, "--pipe_fd", str(w)], pass_fds=[w], stdout=fo, stderr=fe,
+                                env=dict(os.environ, FFS_DEV_KNOBS="1", FFS_CLI_TIMING="1"))
         os.close(w)
         n_lines = 0
         with os.fdopen(r) as f:
@@ -56,10 +57,11 @@ def run(exe, args, workdir):
     wall = time.perf_counter() - t0
     out = (workdir / "stdout.txt").read_text(errors="replace")
     err = (workdir / "stderr.txt").read_text(errors="replace")
+    wt = re.search(r"worker time.*", out)
     m = re.search(r"(\d+) images in ([0-9.]+) s \(([0-9.]+) GBps\) \(([0-9.]+) fps\)", out)
     return {"rc": proc.returncode, "json_lines": n_lines, "images": int(m.group(1)) if m else 0,
             "seconds": float(m.group(2)) if m else None, "fps": float(m.group(4)) if m else None,
-            "wall_seconds_with_startup": wall, "stderr": err[-300:]}
+            "wall_seconds_with_startup": wall, "worker_time": wt.group(0) if wt else None, "stderr": err[-300:]}
 
 
 def main():
@@ -111,7 +113,7 @@ def main():
             for t in args.threads:
                 r = run("spotfinder", [path, "--threads", str(t), "--detector", det], base)
                 r.update(source=source, threads=t)
-                print(source, t, r["fps"], r["rc"], file=sys.stderr)
+                print(source, t, r["fps"], r["rc"], r["worker_time"], file=sys.stderr)
                 out["runs"].append(r)
     finally:
         shutil.rmtree(base, ignore_errors=True)
