@@ -91,22 +91,66 @@ __device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, int 
     if (lane < len - done) dst[done + lane] = src[done + lane];
 }
 
-// Decode one raw LZ4 block from in[0..in_len) (global memory, read through L1: the parse is
-// sequential, so every 128-byte line serves many sequences) to out[0..out_len) (shared).
-// Returns false on malformed input.  All lanes take the same path.
+// Literal runs longer than the parse window: global -> shared, four rounds of loads in flight
+// (the source is read-only global memory, so no round waits for the previous round's stores).
+__device__ __forceinline__ void warp_copy_in(uint8_t* dst, const uint8_t* __restrict__ src, int len, int lane) {
+    if (len <= 32) {
+        if (lane < len) dst[lane] = src[lane];
+        return;
+    }
+    const int head = (int)((4u - ((uint32_t)reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u);
+    if (lane < head) dst[lane] = src[lane];
+    const int nwords = (len - head) >> 2;
+    const uint8_t* s = src + head;
+    const uint32_t sh = ((uint32_t)reinterpret_cast<uintptr_t>(s) & 3u) * 8u;
+    const uint32_t* sa = reinterpret_cast<const uint32_t*>(s - (sh >> 3));
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst + head);
+    for (int base = 0; base < nwords; base += 128) {  // uniform trip count
+        uint32_t lo[4], hi[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int w = base + 32 * u + lane;
+            lo[u] = hi[u] = 0;
+            if (w < nwords) {
+                lo[u] = __ldg(sa + w);
+                hi[u] = __ldg(sa + w + 1);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int w = base + 32 * u + lane;
+            if (w < nwords) d[w] = __funnelshift_r(lo[u], hi[u], sh);
+        }
+    }
+    const int done = head + (nwords << 2);
+    if (lane < len - done) dst[done + lane] = src[done + lane];
+}
+
+// Decode one raw LZ4 block from in[0..in_len) (global memory, read through L1) to
+// out[0..out_len) (shared).  Returns false on malformed input.  All lanes take the same path.
+//
+// The parse is a serial chain (token -> literal length -> offset -> match length -> next token),
+// so what matters is the latency and the instruction count of one sequence:
+//   * the 32 bytes that follow the parse position sit in a register window, one byte per lane
+//     (ONE coalesced load per sequence, issued as soon as the next position is known, i.e.
+//     before the match copy runs); token, offset and the first length-extension byte come out of
+//     it by warp shuffles, and literal runs of up to 14 bytes are stored straight from it;
+//   * matches of up to 128 bytes (the bulk) are copied as at most 4 bytes per lane, no
+//     alignment prologue; longer ones take the word / pattern copies below.
 __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* __restrict__ in, int in_len, uint8_t* out,
                                                 int out_len, int lane) {
+    constexpr unsigned FULL = 0xffffffffu;
     int ip = 0, op = 0;
-    // length extension bytes: 255, 255, ..., b < 255
+    // length extension bytes from ip on: 255, 255, ..., b < 255  (long lengths only)
     auto extend = [&](int& len) -> bool {
         for (;;) {
             const int idx = ip + lane;
             const uint32_t b = idx < in_len ? in[idx] : 0u;
-            const unsigned nz = __ballot_sync(0xffffffffu, b != 255u);
+            const unsigned nz = __ballot_sync(FULL, b != 255u);
             if (nz) {
                 const int first = __ffs(nz) - 1;
                 if (ip + first >= in_len) return false;
-                len += 255 * first + (int)__shfl_sync(0xffffffffu, b, first);
+                len += 255 * first + (int)__shfl_sync(FULL, b, first);
                 ip += first + 1;
                 return true;
             }
@@ -115,25 +159,89 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* __restrict__ in, 
             if (ip >= in_len) return false;
         }
     };
+    auto load_win = [&](int p) -> uint32_t {
+        const int i = p + lane;
+        return i < in_len ? (uint32_t)in[i] : 0u;
+    };
+    // first touch of the payload: all of its lines at once instead of one miss after the other
+    for (int o = lane * 128; o < in_len; o += 32 * 128) {
+        uint32_t sink;
+        asm volatile("ld.global.ca.u8 %0, [%1];" : "=r"(sink) : "l"(in + o));
+    }
+    uint32_t win = load_win(0);  // byte ip + lane of the input, 0 beyond its end
     while (ip < in_len) {
-        const uint32_t token = in[ip++];
-        int lit = token >> 4;
-        if (lit == 15 && !extend(lit)) return false;
-        if (lit > in_len - ip || lit > out_len - op) return false;
-        if (lit) warp_copy<false>(out + op, in + ip, lit, lane);
+        const uint32_t token = __shfl_sync(FULL, win, 0);
+        int lit = (int)(token >> 4);
+        int mlen = (int)(token & 15u);
+        const bool in_win = lit < 15;  // token, literals, offset and one extension byte: lanes 0 .. lit + 3 <= 17
+        // issued early, used after the literals (lanes beyond the input hold 0)
+        const uint32_t o0 = __shfl_sync(FULL, win, (lit + 1) & 31);
+        const uint32_t o1 = __shfl_sync(FULL, win, (lit + 2) & 31);
+        const uint32_t e0 = __shfl_sync(FULL, win, (lit + 3) & 31);
+        ++ip;
+        if (in_win) {
+            if (lit > in_len - ip || lit > out_len - op) return false;
+            if (lane >= 1 && lane <= lit) out[op + lane - 1] = (uint8_t)win;
+        } else {
+            if (!extend(lit)) return false;
+            if (lit > in_len - ip || lit > out_len - op) return false;
+            warp_copy_in(out + op, in + ip, lit, lane);
+        }
         ip += lit;
         op += lit;
         if (ip >= in_len) break;  // the last sequence has no match
         if (in_len - ip < 2) return false;
-        const int offset = in[ip] | (in[ip + 1] << 8);
+        int offset;
+        if (in_win) offset = (int)(o0 | (o1 << 8));
+        else offset = in[ip] | (in[ip + 1] << 8);
         ip += 2;
-        int mlen = token & 15;
-        if (mlen == 15 && !extend(mlen)) return false;
+        if (mlen == 15) {
+            if (in_win && e0 != 255u) {
+                if (ip >= in_len) return false;
+                mlen += (int)e0;
+                ++ip;
+            } else if (!extend(mlen)) {
+                return false;
+            }
+        }
         mlen += 4;
         if (offset == 0 || offset > op || mlen > out_len - op) return false;
+        win = load_win(ip);  // the next sequence's window: in flight while the match is copied
         if (lit) __syncwarp();  // literals just written may be the match source
         uint8_t* dst = out + op;
-        if (offset >= mlen) {
+        if (mlen <= 128) {
+            if (offset >= mlen) {  // no overlap: <= 4 bytes per lane, loads before stores
+                const uint8_t* s = dst - offset;
+                uint32_t b[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) b[u] = (lane + 32 * u < mlen) ? (uint32_t)s[lane + 32 * u] : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (lane + 32 * u < mlen) dst[lane + 32 * u] = (uint8_t)b[u];
+            } else if ((offset & (offset - 1)) == 0 && offset <= 32) {
+                // run with a power-of-two period: every byte a lane writes is the same source byte
+                const uint8_t v = dst[(lane & (offset - 1)) - offset];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (lane + 32 * u < mlen) dst[lane + 32 * u] = v;
+            } else if (offset > 32) {
+                // overlapping, period longer than a round: a round reads what earlier rounds wrote
+                for (int base = 0; base < mlen; base += 32) {  // uniform trip count
+                    const int k = base + lane;
+                    if (k < mlen) dst[k] = dst[k - offset];
+                    __syncwarp();
+                }
+            } else {
+                // short period: the periodic sequence it denotes
+                const int step = 32 % offset;
+                int km = lane % offset;
+                for (int k = lane; k < mlen; k += 32) {
+                    dst[k] = dst[km - offset];
+                    km += step;
+                    if (km >= offset) km -= offset;
+                }
+            }
+        } else if (offset >= mlen) {
             warp_copy<false>(dst, dst - offset, mlen, lane);
         } else if (offset == 1 || offset == 2 || offset == 4) {
             // run: the 4-byte pattern seen from an aligned word is the same for every word
@@ -169,6 +277,18 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* __restrict__ in, 
     }
     return op == out_len;
 }
+
+#ifdef BSLZ4_TIMELINE  // developer build (make variant EXTRA=-DBSLZ4_TIMELINE): per-warp {start, LZ4 done, end, block | smid << 16}
+__device__ uint4 g_bslz4_timeline[16384];
+__device__ __forceinline__ uint32_t tl_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return (uint32_t)t;
+}
+extern "C" int ffs_debug_bslz4_timeline(void* out, size_t bytes) {
+    return (int)cudaMemcpyFromSymbol(out, g_bslz4_timeline, bytes < sizeof(g_bslz4_timeline) ? bytes : sizeof(g_bslz4_timeline));
+}
+#endif
 
 // grid: ceil(n_blocks / WARPS) CTAs of WARPS warps; dynamic smem WARPS * kBslz4SmemPerWarp.
 template <typename PixelT, int WARPS>
@@ -206,12 +326,18 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
         return;
     }
     const uint8_t* in = a.chunk + blk.x;
+#ifdef BSLZ4_TIMELINE
+    const uint32_t tl0 = tl_now();
+#endif
     // 2. LZ4
     if (!lz4_warp_decode(in, in_len, out, out_len, lane)) {
         if (lane == 0) atomicExch(a.status, 2u);
         return;
     }
     __syncwarp();
+#ifdef BSLZ4_TIMELINE
+    const uint32_t tl1 = tl_now();
+#endif
     // 3. bit planes -> pixels.  Plane (byte j, bit k) is row 8j+k, n_el/8 bytes per row;
     //    column c holds bit (e & 7) of elements e = 8c .. 8c+7.
     const int row_bytes = n_el >> 3;
@@ -298,6 +424,13 @@ __global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Arg
         }
       }
     }
+#ifdef BSLZ4_TIMELINE
+    if (lane == 0 && w_id < 16384) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        g_bslz4_timeline[w_id] = make_uint4(tl0, tl1, tl_now(), b | (smid << 16));
+    }
+#endif
 }
 
 }  // namespace ffsb
