@@ -290,9 +290,12 @@ extern "C" int ffs_debug_bslz4_timeline(void* out, size_t bytes) {
 }
 #endif
 
+#ifndef BSLZ4_MIN_CTAS
+#define BSLZ4_MIN_CTAS 1  // resident CTAs per SM the kernel is compiled for (register cap); shared memory allows 13 of 2 warps
+#endif
 // grid: ceil(n_blocks / WARPS) CTAs of WARPS warps; dynamic smem WARPS * kBslz4SmemPerWarp.
 template <typename PixelT, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) bslz4_decode_kernel(const Bslz4Args a) {
+__global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kernel(const Bslz4Args a) {
     extern __shared__ __align__(16) uint8_t bsmem[];
     const Bslz4Dyn dyn = *a.dyn;
     const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn + 1);

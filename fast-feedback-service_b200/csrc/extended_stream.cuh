@@ -370,19 +370,27 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
                 // left 65 % of the rows unpruned: every strip that holds a module-gap or image edge.)
                 const uint32_t vb = hi3 & 0xffu;  // validity of the centre row's pixels
                 {
-                    bool maybe = flagged;
+                    // 4 instructions per pixel (IMAD, IADD, IMAD, ISETP.OR): validity is not tested per
+                    // pixel.  Full groups: a group without a valid pixel is skipped as a whole, and a
+                    // (rare) partly valid one can only send the row to the per-pixel path, which tests
+                    // validity itself.  Other groups: an invalid pixel's count is masked to m = 0 first,
+                    // so its test reads 0 > x (x + K(0)) and never holds.
+                    bool any = false;
                     if (mq3.x == kFull4 && mq3.y == kFull4) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)  // (without the validity test gap pixels send rows to the
-                            // slow path: 55.3 vs 52.5 us per frame, u32 78.5 vs 69.7, same box)
-                            maybe |= ((vb >> j) & 1u) && (49u * Hy[j] > Hx[j] * (Hx[j] + kf49));
+                        for (int j = 0; j < 8; ++j) any |= 49u * Hy[j] > Hx[j] * (Hx[j] + kf49);
+                        any = any && vb != 0u;
                     } else {
+                        const uint32_t zlo = (vb & 0xfu) * 0x10204080u, zhi = (vb >> 4) * 0x10204080u;
+                        const uint32_t ma = mq3.x & ptx::prmt(zlo, 0u, 0xba98u) & 0x3f3f3f3fu;
+                        const uint32_t mb = mq3.y & ptx::prmt(zhi, 0u, 0xba98u) & 0x3f3f3f3fu;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            const uint32_t mj = ((j < 4 ? mq3.x : mq3.y) >> (8 * (j & 3))) & 0x3fu;
-                            maybe |= ((vb >> j) & 1u) && (mj * Hy[j] > Hx[j] * (Hx[j] + ktabi[mj]));
+                            const uint32_t mj = ((j < 4 ? ma : mb) >> (8 * (j & 3))) & 0xffu;
+                            any |= mj * Hy[j] > Hx[j] * (Hx[j] + ktabi[mj]);
                         }
                     }
+                    const bool maybe = flagged || any;
                     if (__ballot_sync(0xffffffffu, out_lane && maybe) == 0u) {
                         hi3 = hi2; hi2 = hi1; hi1 = info;
                         mq3 = mq2; mq2 = mq1; mq1 = mq0;
