@@ -164,10 +164,12 @@ __device__ __forceinline__ bool lz4_warp_decode(const uint8_t* __restrict__ in, 
         return i < in_len ? (uint32_t)in[i] : 0u;
     };
     // first touch of the payload: all of its lines at once instead of one miss after the other
+#pragma nv_diag_suppress 550  // the loaded value is deliberately never read (nothing waits for it)
     for (int o = lane * 128; o < in_len; o += 32 * 128) {
         uint32_t sink;
         asm volatile("ld.global.ca.u8 %0, [%1];" : "=r"(sink) : "l"(in + o));
     }
+#pragma nv_diag_default 550
     uint32_t win = load_win(0);  // byte ip + lane of the input, 0 beyond its end
     while (ip < in_len) {
         const uint32_t token = __shfl_sync(FULL, win, 0);

@@ -180,16 +180,22 @@ __device__ __forceinline__ void fused_load_row(const uint8_t* pimg, const uint8_
     } else {
         const uint4 ra = ptx::lds128(pimg);
         const uint4 rb = ptx::lds128(pimg + 16);
-        const uint32_t r[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+        // lut_s (32-bit pixels): 16-entry table, entry n = four AND masks {~0 per set bit of the nibble n};
+        // 256-byte aligned, so (index << 4) | base is one LOP3
+        const uint4 mlo = ptx::lds128_s(((info << 4) & 0xf0u) | lut_s);
+        const uint4 mhi = ptx::lds128_s((info & 0xf0u) | lut_s);
+        const uint32_t v[8] = {ra.x & mlo.x, ra.y & mlo.y, ra.z & mlo.z, ra.w & mlo.w,
+                               rb.x & mhi.x, rb.y & mhi.y, rb.z & mhi.z, rb.w & mhi.w};
         uint32_t cl[8];
-        vmax = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const uint32_t v = (info & (1u << j)) ? r[j] : 0u;
-            vmax = max(vmax, v);
-            // pixels >= 2^24 are not counted by the reference (standalone.cc:90), nor are pixels
-            // above the trusted range: they add 0  (vlim = min(trusted_max, 2^24 - 1))
-            cl[j] = v <= vlim ? min(v, CL) : 0u;
+        for (int j = 0; j < 8; ++j) cl[j] = min(v[j], CL);
+        vmax = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
+        // pixels >= 2^24 are not counted by the reference (standalone.cc:90), nor are pixels
+        // above the trusted range: they add 0  (vlim = min(trusted_max, 2^24 - 1)).  Rare: only a
+        // group that holds one takes this branch.
+        if (vmax > vlim) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) cl[j] = v[j] <= vlim ? cl[j] : 0u;
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) c[k] = cl[2 * k] | (cl[2 * k + 1] << 16);
@@ -366,12 +372,20 @@ __global__ void __launch_bounds__(WARPS * 32, FusedGeo<PixelT>::MIN_WARPS_PER_SM
     // parameter turns every field access into a generic load from the parameter window
     // (long-scoreboard latency on each call), a shared-memory copy is one LDS away.
     __shared__ ThreshArgs sa;
-    __shared__ __align__(128) uint2 mask_lut[16];
+    // 16-bit: entry n = two words {0xffff per set bit of the nibble n} & {CLAMP, CLAMP} (128 B);
+    // 32-bit: four AND masks (256 B).  Sized per pixel type: the 16-bit kernel's 4 CTAs per SM leave
+    // no room for another kilobyte of static shared memory.
+    constexpr int kLutBytes = sizeof(PixelT) == 2 ? 128 : 256;
+    __shared__ __align__(kLutBytes) uint8_t mask_lut[kLutBytes];
     if (threadIdx.x < 16) {
         constexpr uint32_t CL = G::CLAMP;
         const uint32_t n = threadIdx.x;
-        mask_lut[n] = make_uint2(((n & 1u) ? CL : 0u) | ((n & 2u) ? CL << 16 : 0u),
-                                 ((n & 4u) ? CL : 0u) | ((n & 8u) ? CL << 16 : 0u));
+        if constexpr (sizeof(PixelT) == 2)
+            reinterpret_cast<uint2*>(mask_lut)[n] = make_uint2(((n & 1u) ? CL : 0u) | ((n & 2u) ? CL << 16 : 0u),
+                                                               ((n & 4u) ? CL : 0u) | ((n & 8u) ? CL << 16 : 0u));
+        else
+            reinterpret_cast<uint4*>(mask_lut)[n] =
+              make_uint4((n & 1u) ? ~0u : 0u, (n & 2u) ? ~0u : 0u, (n & 4u) ? ~0u : 0u, (n & 8u) ? ~0u : 0u);
     }
     uint32_t lut_s;  // opaque move: keeps the address in a register instead of re-deriving it per stage
     asm volatile("mov.u32 %0, %1;" : "=r"(lut_s) : "r"(ptx::smem_u32(mask_lut)));

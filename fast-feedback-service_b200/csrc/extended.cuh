@@ -51,6 +51,10 @@ __global__ void __launch_bounds__(256) erode_kernel(const ErodeArgs a) {
         uint32_t core = 0;
         if (in_plane && wi > last_word) {
             B[t] = 0;
+        } else if (in_plane && (D[t] & (wi == last_word ? last_valid : 0xffffffffu)) == 0u) {
+            // no D pixel in this word, so no core pixel either (the core is a subset of D): the 5x5
+            // neighbourhood is not read.  D is sparse -- on background nearly every word ends here.
+            B[t] = a.mask_bits[t] & (wi == last_word ? last_valid : 0xffffffffu);
         } else if (in_plane) {
             core = 0xffffffffu;
             // out-of-image pixels are ignored by the distance transform: they read as "true"

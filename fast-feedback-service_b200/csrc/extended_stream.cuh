@@ -187,6 +187,12 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
     // proves a <= c, i.e. D = 0, in exact integer arithmetic (see the row prune below)
     __shared__ uint32_t ktabi[64];
     __shared__ ThreshArgs sa;  // the out-of-line paths read their arguments from here (see dispersion_fused.cuh)
+    // 32-bit front end: validity nibble -> four AND masks (one LDS.128 instead of a test + select per pixel)
+    __shared__ __align__(16) uint4 vmask_lut[16];
+    if (threadIdx.x < 16) {
+        const uint32_t n = threadIdx.x;
+        vmask_lut[n] = make_uint4((n & 1u) ? ~0u : 0u, (n & 2u) ? ~0u : 0u, (n & 4u) ? ~0u : 0u, (n & 8u) ? ~0u : 0u);
+    }
     for (int t = threadIdx.x; t < (int)(sizeof(ThreshArgs) / 4); t += WARPS * 32)
         reinterpret_cast<uint32_t*>(&sa)[t] = reinterpret_cast<const uint32_t*>(&a)[t];
     for (int t = threadIdx.x; t < 64; t += WARPS * 32) {
@@ -264,6 +270,8 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
     const int pimg_off = lane * PPL * (int)sizeof(PixelT);
     const int pinfo_off = G::IMG_STAGE_BYTES + (info_b - info_b0) + 4 * lane;
 
+    // this lane's 8 window counts in load row i (read only where the group info says "not full")
+    const uint8_t* mrow = a.mcount + (ptrdiff_t)y_first * (ptrdiff_t)a.m_pitch + 8 * (ptrdiff_t)group;
     int s = 0;
     uint32_t phase = 0;
     for (int g = 0; g < n_groups; ++g) {
@@ -278,7 +286,8 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
             const uint32_t info = *reinterpret_cast<const uint32_t*>(st + pinfo_off + u * E::INFO4_ROW_BYTES);
             uint2 mq0 = make_uint2(kFull4, kFull4);
             if ((info & 0xffu) && !(info & 0x4000u))  // (rows / groups outside the image are zero-filled: info == 0)
-                mq0 = *reinterpret_cast<const uint2*>(a.mcount + (size_t)(y_first + i) * a.m_pitch + 8 * (size_t)group);
+                mq0 = *reinterpret_cast<const uint2*>(mrow);
+            mrow += a.m_pitch;
             uint32_t c[4];
             bool big;
             if constexpr (sizeof(PixelT) == 2) {
@@ -298,14 +307,13 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
             } else {
                 const uint4 ra = ptx::lds128(st + u * G::IMG_ROW_BYTES + pimg_off);
                 const uint4 rb = ptx::lds128(st + u * G::IMG_ROW_BYTES + pimg_off + 16);
-                const uint32_t r[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
-                uint32_t cl[8], vmax = 0;
+                const uint4 mlo = vmask_lut[info & 0xfu], mhi = vmask_lut[(info >> 4) & 0xfu];
+                const uint32_t v[8] = {ra.x & mlo.x, ra.y & mlo.y, ra.z & mlo.z, ra.w & mlo.w,
+                                       rb.x & mhi.x, rb.y & mhi.y, rb.z & mhi.z, rb.w & mhi.w};
+                uint32_t cl[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint32_t v = (info & (1u << j)) ? r[j] : 0u;
-                    vmax = max(vmax, v);
-                    cl[j] = min(v, CL);
-                }
+                for (int j = 0; j < 8; ++j) cl[j] = min(v[j], CL);
+                const uint32_t vmax = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
                 big = vmax > CL;  // includes uncounted pixels >= 2^24
 #pragma unroll
                 for (int k = 0; k < 4; ++k) c[k] = cl[2 * k] | (cl[2 * k + 1] << 16);
@@ -376,7 +384,9 @@ __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
                     // validity itself.  Other groups: an invalid pixel's count is masked to m = 0 first,
                     // so its test reads 0 > x (x + K(0)) and never holds.
                     bool any = false;
-                    if (mq3.x == kFull4 && mq3.y == kFull4) {
+                    // warp-uniform choice: the general path is right for full groups too (m = 49), so a
+                    // row with one group next to a gap runs it alone instead of both paths diverged
+                    if (__all_sync(0xffffffffu, mq3.x == kFull4 && mq3.y == kFull4)) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) any |= 49u * Hy[j] > Hx[j] * (Hx[j] + kf49);
                         any = any && vb != 0u;

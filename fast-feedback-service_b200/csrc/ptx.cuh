@@ -96,6 +96,12 @@ __device__ __forceinline__ uint4 lds128(const void* p) {
 }
 
 // 8-byte shared-memory load from a 32-bit shared address
+__device__ __forceinline__ uint4 lds128_s(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
 __device__ __forceinline__ uint2 lds64_s(uint32_t addr) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
