@@ -293,7 +293,8 @@ extern "C" int ffs_debug_bslz4_timeline(void* out, size_t bytes) {
 #endif
 
 #ifndef BSLZ4_MIN_CTAS
-#define BSLZ4_MIN_CTAS 1  // resident CTAs per SM the kernel is compiled for (register cap); shared memory allows 13 of 2 warps
+#define BSLZ4_MIN_CTAS 13  // resident CTAs per SM the kernel is compiled for: shared memory allows 13 of 2 warps (<= 72 registers; left
+                           // to itself ptxas takes 82-96 and 10 CTAs fit: same speed, 61.5 vs 62.7 us u16, 93.1 vs 92.8 u32)
 #endif
 // grid: ceil(n_blocks / WARPS) CTAs of WARPS warps; dynamic smem WARPS * kBslz4SmemPerWarp.
 template <typename PixelT, int WARPS>

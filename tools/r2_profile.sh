@@ -10,6 +10,7 @@ timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu --no-extra > $O/b2.jso
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $O/launches_bench_steps2.csv python bench.py --steps 2 --warmup 1 --no-cpu --no-extra > $O/ncu_launches.log 2>&1
 BATCHES=32 SLOTS=32 timeout 600 $NCU -k regex:fused_dispersion -s 3 -c 1 -o $O/fused_b32 python tools/bench_threshold.py > $O/n1.log 2>&1
 BATCHES=1 SLOTS=2 timeout 600 $NCU -k regex:fused_dispersion -s 3 -c 1 -o $O/fused_b1 python tools/bench_threshold.py > $O/n2.log 2>&1
+BPP=4 ALGO=dispersion_extended BATCHES=16 SLOTS=16 timeout 600 $NCU -k regex:ext_pass1 -s 3 -c 1 -o $O/ext_pass1_u32 python tools/bench_threshold.py > $O/n3b.log 2>&1
 ALGO=dispersion_extended BATCHES=16 SLOTS=16 timeout 600 $NCU -k regex:ext_pass1 -s 3 -c 1 -o $O/ext_pass1 python tools/bench_threshold.py > $O/n3.log 2>&1
 ALGO=dispersion_extended BATCHES=16 SLOTS=16 timeout 600 $NCU -k regex:erode_kernel -s 3 -c 1 -o $O/erode python tools/bench_threshold.py > $O/n4.log 2>&1
 ALGO=dispersion_extended BATCHES=16 SLOTS=16 timeout 600 $NCU -k regex:final_kernel -s 3 -c 1 -o $O/final python tools/bench_threshold.py > $O/n5.log 2>&1
