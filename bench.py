@@ -674,7 +674,8 @@ def run_gpu_arm(args):
             alg = algorithmic_bytes_per_frame(g, dtype) * B
             achieved = alg / (k_avg * 1e-3) / 1e9
             ext = cfg["algorithm"] != "dispersion"
-            traffic = ncu_traffic_per_frame("ext_dram_bytes_per_frame" if ext else "fused_dram_bytes_per_frame")
+            ext_key = "ext_u32_dram_bytes_per_frame" if np.dtype(dtype).itemsize == 4 else "ext_u16_dram_bytes_per_frame"
+            traffic = ncu_traffic_per_frame(ext_key if ext else "fused_dram_bytes_per_frame")
             h2d_gbs = r["n_e2e"] * frame_bytes / t_e2e / 1e9
             ceil_gbs, ceil_src = h2d_ceiling(world)
             out = {
@@ -724,7 +725,7 @@ def run_gpu_arm(args):
             if rank == 0:
                 alg3 = algorithmic_bytes_per_frame(c3["geom"], c3["dtype"]) * r3["B"]
                 ach3 = alg3 / (red3[2] * 1e-3) / 1e9
-                tr3 = ncu_traffic_per_frame("ext_dram_bytes_per_frame")
+                tr3 = ncu_traffic_per_frame("ext_u32_dram_bytes_per_frame")
                 extra["eiger16m_u32_ext"] = {
                     "value": world * r3["B"] * r3["steps"] / (red3[0] * 1e-3), "unit": "frames/s",
                     "e2e": world * r3["n_e2e"] / (red3[1] / 1e3), "frames_per_step": r3["B"], "steps": r3["steps"],
