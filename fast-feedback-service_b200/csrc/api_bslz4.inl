@@ -178,6 +178,10 @@ extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, si
     // the two uploads whose sizes change from frame to frame stay outside the slot's graph
     FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, chunk, chunk_bytes,
                               cudaMemcpyHostToDevice, st));
+#ifdef BSLZ4_EXP_SKIP_TABLE  // timing experiment only: the slot keeps the block table of its previous chunk
+    static const bool skip_table = env_int("FFS_SKIP_TABLE_COPY", 0) != 0;
+    if (!skip_table)
+#endif
     FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
                               c->h_blocks + (size_t)slot * c->blocks_stride,
                               sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * dyn.n_blocks,
