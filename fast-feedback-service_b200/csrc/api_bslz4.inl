@@ -5,6 +5,20 @@ static inline uint32_t be32h(const uint8_t* p) {
     return (uint32_t)p[0] << 24 | (uint32_t)p[1] << 16 | (uint32_t)p[2] << 8 | p[3];
 }
 
+// the slot's chunk in the pinned host buffer / in device memory (its table ends right in front of it)
+static inline uint8_t* bslz4_h_chunk(ffs_ctx* c, int slot) { return c->h_chunks + (size_t)slot * c->chunk_stride + c->table_cap; }
+static inline uint8_t* bslz4_d_chunk(ffs_ctx* c, int slot) { return c->d_chunks + (size_t)slot * c->chunk_stride + c->table_cap; }
+// offset, from the chunk's start backwards, at which the upload begins (16-byte aligned)
+static inline size_t bslz4_table_bytes(uint32_t n_blocks) {
+    return round_up(sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * (size_t)n_blocks, 16);
+}
+// one copy: block table + chunk
+static inline cudaError_t bslz4_upload(ffs_ctx* c, int slot, uint32_t n_blocks, size_t chunk_bytes, cudaStream_t st) {
+    const size_t tb = bslz4_table_bytes(n_blocks);
+    return cudaMemcpyAsync(bslz4_d_chunk(c, slot) - tb, bslz4_h_chunk(c, slot) - tb, tb + chunk_bytes,
+                           cudaMemcpyHostToDevice, st);
+}
+
 static int bslz4_setup(ffs_ctx* c) {
     if (c->h_chunks) return FFS_OK;
     const size_t S = c->p.n_slots;
@@ -17,12 +31,12 @@ static int bslz4_setup(ffs_ctx* c) {
     const size_t frame_bytes = n * es;
     c->chunk_cap = round_up(frame_bytes + frame_bytes / 255 + 20 * (size_t)c->max_blocks + 12 + 64, 256);
     FFS_CK(c, cudaSetDevice(c->p.device));
-    FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_cap * S, cudaHostAllocDefault));
-    FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_cap * S + 64));
-    // Bslz4Dyn | uint2 {offset, length} per block | uint32 work order (longest payload first)
-    c->blocks_stride = round_up(sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * c->max_blocks, 16);
-    FFS_CK(c, cudaHostAlloc(&c->h_blocks, c->blocks_stride * S, cudaHostAllocDefault));
-    FFS_CK(c, cudaMalloc(&c->d_blocks, c->blocks_stride * S));
+    // in front of every chunk: uint32 work order (longest payload first) | uint2 {offset, length} per
+    // block | Bslz4Dyn, written backwards from the chunk's start (context.cuh)
+    c->table_cap = round_up(sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * (size_t)c->max_blocks, 256);
+    c->chunk_stride = c->table_cap + c->chunk_cap;
+    FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_stride * S, cudaHostAllocDefault));
+    FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_stride * S + 64));
     FFS_CK(c, cudaMalloc(&c->d_dec_status, sizeof(unsigned) * S));
     FFS_CK(c, cudaHostAlloc(&c->h_dec_status, sizeof(unsigned) * S, cudaHostAllocDefault));
     memset(c->h_dec_status, 0, sizeof(unsigned) * S);
@@ -32,8 +46,6 @@ static int bslz4_setup(ffs_ctx* c) {
 static void bslz4_teardown(ffs_ctx* c) {
     cudaFreeHost(c->h_chunks);
     cudaFree(c->d_chunks);
-    cudaFreeHost(c->h_blocks);
-    cudaFree(c->d_blocks);
     cudaFree(c->d_dec_status);
     cudaFreeHost(c->h_dec_status);
 }
@@ -53,8 +65,8 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
     last -= last % 8;
     const size_t n_blocks = full + (last ? 1 : 0);
     if (n_blocks > c->max_blocks) return FFS_ERR_FORMAT;
-    Bslz4Dyn* hdr = reinterpret_cast<Bslz4Dyn*>(c->h_blocks + (size_t)slot * c->blocks_stride);
-    uint2* tab = reinterpret_cast<uint2*>(hdr + 1);
+    Bslz4Dyn* hdr = reinterpret_cast<Bslz4Dyn*>(bslz4_h_chunk(c, slot)) - 1;
+    uint2* tab = reinterpret_cast<uint2*>(hdr) - n_blocks;
     size_t pos = 12;
     for (size_t b = 0; b < n_blocks; ++b) {
         if (len - pos < 4) return FFS_ERR_FORMAT;
@@ -78,7 +90,7 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
     // the kernel is ~1.15 waves of warps, so the blocks that start last decide when it ends: make those
     // the cheapest ones (module-gap blocks compress to a few bytes).  Counting sort, O(n_blocks).
     {
-        uint32_t* order = reinterpret_cast<uint32_t*>(tab + n_blocks);
+        uint32_t* order = reinterpret_cast<uint32_t*>(tab) - n_blocks;
         constexpr int kBuckets = 64;
         uint32_t start[kBuckets + 1] = {};
         auto bucket = [](uint32_t clen) { return kBuckets - 1 - (int)std::min<uint32_t>(clen >> 7, kBuckets - 1); };
@@ -92,8 +104,8 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
 static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st) {
     constexpr int kWarps = 2;
     Bslz4Args a{};
-    a.chunk = c->d_chunks + (size_t)slot * c->chunk_cap;
-    a.dyn = reinterpret_cast<const Bslz4Dyn*>(c->d_blocks + (size_t)slot * c->blocks_stride);
+    a.chunk = bslz4_d_chunk(c, slot);
+    a.dyn = reinterpret_cast<const Bslz4Dyn*>(a.chunk) - 1;
     a.frame = c->d_frames + (size_t)slot * c->frame_stride;
     a.pitch = c->pitch;
     a.width = c->p.width;
@@ -133,7 +145,7 @@ extern "C" int ffs_acquire_compressed(ffs_ctx* c, int* slot, void** pinned_chunk
     void* frame = nullptr;
     int rc = ffs_acquire(c, slot, &frame);
     if (rc) return rc;
-    *pinned_chunk = c->h_chunks + (size_t)*slot * c->chunk_cap;
+    *pinned_chunk = bslz4_h_chunk(c, *slot);
     if (capacity) *capacity = c->chunk_cap;
     return FFS_OK;
 }
@@ -148,7 +160,7 @@ extern "C" int ffs_slot_buffers(ffs_ctx* c, int slot, void** pinned_pixels, void
     }
     if (pinned_pixels)
         *pinned_pixels = c->h_frames + (size_t)slot * ((size_t)c->p.width * c->p.height * c->p.bytes_per_pixel);
-    if (pinned_chunk) *pinned_chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
+    if (pinned_chunk) *pinned_chunk = bslz4_h_chunk(c, slot);
     if (chunk_capacity) *chunk_capacity = c->chunk_cap;
     return FFS_OK;
 }
@@ -159,7 +171,7 @@ extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, si
     // the chunk was DMA-ed into the buffer rather than written by this core) runs outside the
     // context lock: the slot belongs to the caller until it is submitted, so producer threads
     // index their chunks in parallel.
-    const uint8_t* chunk = c->h_chunks + (size_t)slot * c->chunk_cap;
+    const uint8_t* chunk = bslz4_h_chunk(c, slot);
     Bslz4Dyn dyn{};
     int rc = bslz4_index(c, slot, chunk, chunk_bytes, dyn);
     std::unique_lock<std::mutex> lk(c->mu);
@@ -175,17 +187,8 @@ extern "C" int ffs_submit_compressed(ffs_ctx* c, int slot, uint64_t frame_id, si
         if (!s.t_ev[0]) FFS_CK(c, cudaEventCreate(&s.t_ev[0]));
         FFS_CK(c, cudaEventRecord(s.t_ev[0], st));
     }
-    // the two uploads whose sizes change from frame to frame stay outside the slot's graph
-    FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, chunk, chunk_bytes,
-                              cudaMemcpyHostToDevice, st));
-#ifdef BSLZ4_EXP_SKIP_TABLE  // timing experiment only: the slot keeps the block table of its previous chunk
-    static const bool skip_table = env_int("FFS_SKIP_TABLE_COPY", 0) != 0;
-    if (!skip_table)
-#endif
-    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
-                              c->h_blocks + (size_t)slot * c->blocks_stride,
-                              sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * dyn.n_blocks,
-                              cudaMemcpyHostToDevice, st));
+    // the upload, whose size changes from frame to frame, stays outside the slot's graph
+    FFS_CK(c, bslz4_upload(c, slot, dyn.n_blocks, chunk_bytes, st));
     s.compressed = true;
     return submit_tail(c, slot, 1, dyn.n_blocks, frame_id, st);
 }
@@ -197,18 +200,14 @@ extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, 
     int rc = bslz4_setup(c);
     if (rc) return rc;
     if (chunk_bytes > c->chunk_cap) return FFS_ERR_FORMAT;
-    uint8_t* h = c->h_chunks + (size_t)slot * c->chunk_cap;
+    uint8_t* h = bslz4_h_chunk(c, slot);
     memcpy(h, chunk, chunk_bytes);
     Bslz4Dyn dyn{};
     rc = bslz4_index(c, slot, h, chunk_bytes, dyn);
     if (rc) return rc;
     FFS_CK(c, cudaSetDevice(c->p.device));
     cudaStream_t st = c->stream;
-    FFS_CK(c, cudaMemcpyAsync(c->d_chunks + (size_t)slot * c->chunk_cap, h, chunk_bytes, cudaMemcpyHostToDevice, st));
-    FFS_CK(c, cudaMemcpyAsync(c->d_blocks + (size_t)slot * c->blocks_stride,
-                              c->h_blocks + (size_t)slot * c->blocks_stride,
-                              sizeof(Bslz4Dyn) + (sizeof(uint2) + sizeof(uint32_t)) * dyn.n_blocks,
-                              cudaMemcpyHostToDevice, st));
+    FFS_CK(c, bslz4_upload(c, slot, dyn.n_blocks, chunk_bytes, st));
     rc = bslz4_launch(c, slot, dyn.n_blocks, st);
     if (rc) return rc;
     unsigned status = 0;

@@ -70,6 +70,9 @@ static int launch_extended(ffs_ctx* c, int first_slot, int n, cudaStream_t st) {
     e.n_frames = n;
     e.slot0 = first_slot;
     e.words_per_row = (int)(c->bits_pitch / 4);
+    // row = t / words_per_row as one multiply-high; exact while t * words_per_row < 2^32 (0: divide)
+    e.inv_wpr = ((uint64_t)e.words_per_row * e.words_per_row * (uint64_t)c->p.height < (1ull << 32))
+                  ? (uint32_t)((1ull << 32) / (uint32_t)e.words_per_row) + 1u : 0u;
     e.mask_bits = reinterpret_cast<const uint32_t*>(c->d_valid_bits);
     e.d_bits = reinterpret_cast<const uint32_t*>(c->d_ext1);
     e.b_bits = reinterpret_cast<uint32_t*>(c->d_ext2);

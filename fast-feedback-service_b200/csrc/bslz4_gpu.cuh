@@ -37,12 +37,13 @@ struct Bslz4Dyn {
     uint32_t tail_elem0;        // index of the first trailing element
     uint32_t pad[2];
 };
-static_assert(sizeof(Bslz4Dyn) == 32, "header precedes the uint2 block table");
+static_assert(sizeof(Bslz4Dyn) == 32, "header sits between the uint2 block table and the chunk");
 
 struct Bslz4Args {
     const uint8_t* chunk;       // device copy of the whole chunk (header + body), 16-byte aligned
-    const Bslz4Dyn* dyn;        // followed by per block: uint2 {payload offset in chunk, payload bytes},
-                                // then uint32 work order[n_blocks]: warp w decodes block order[w]
+    const Bslz4Dyn* dyn;        // = chunk - 32; PRECEDED by per block: uint2 {payload offset in chunk, payload
+                                // bytes}, and before that uint32 work order[n_blocks]: warp w decodes block
+                                // order[w]  (written backwards from the header so one copy uploads table + chunk)
     uint8_t* frame;             // pitched destination
     size_t pitch;
     uint32_t width;
@@ -301,7 +302,7 @@ template <typename PixelT, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kernel(const Bslz4Args a) {
     extern __shared__ __align__(16) uint8_t bsmem[];
     const Bslz4Dyn dyn = *a.dyn;
-    const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn + 1);
+    const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn) - dyn.n_blocks;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t w_id = blockIdx.x * WARPS + warp;
     constexpr int ES = (int)sizeof(PixelT);
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kerne
         reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
     }
     if (w_id >= dyn.n_blocks) return;
-    const uint32_t b = reinterpret_cast<const uint32_t*>(blocks + dyn.n_blocks)[w_id];  // longest payload first
+    const uint32_t b = (reinterpret_cast<const uint32_t*>(blocks) - dyn.n_blocks)[w_id];  // longest payload first
     if (b >= dyn.n_blocks) {
         if (lane == 0) atomicExch(a.status, 3u);
         return;

@@ -105,13 +105,19 @@ struct ffs_ctx {
     uint8_t* d_stage = nullptr;          // n_slots dense device frames (H2D target when pitch != row bytes)
 
     // compressed ingestion (bslz4_gpu.cuh), allocated on first use
-    size_t chunk_cap = 0;             // bytes per slot
+    // Per slot, in the pinned host buffer and in the device buffer alike:
+    //   [ ... unused ... | work order u32[n] | block table uint2[n] | Bslz4Dyn | chunk bytes ... ]
+    //                                                                ^ table_cap - 32   ^ table_cap
+    // The table is written BACKWARDS from the fixed position of its header, so that it ends where the
+    // chunk starts and ONE copy uploads both (a second, 50 KB copy per frame cost 8.6 us of a 146 us
+    // frame period), while the kernel finds the header -- and from n_blocks everything else -- at an
+    // address that never changes (the slot's CUDA graph stays valid).
+    size_t chunk_cap = 0;             // bytes per slot available to the chunk itself
+    size_t table_cap = 0;             // bytes per slot in front of the chunk (header + table for max_blocks)
+    size_t chunk_stride = 0;          // table_cap + chunk_cap
     uint32_t max_blocks = 0;
-    uint8_t* h_chunks = nullptr;      // pinned, n_slots * chunk_cap
+    uint8_t* h_chunks = nullptr;      // pinned, n_slots * chunk_stride
     uint8_t* d_chunks = nullptr;
-    size_t blocks_stride = 0;         // bytes per slot: Bslz4Dyn header + max_blocks * uint2 {offset, length}
-    uint8_t* h_blocks = nullptr;      // pinned
-    uint8_t* d_blocks = nullptr;
     unsigned int* d_dec_status = nullptr;  // n_slots
     unsigned int* h_dec_status = nullptr;  // pinned
 

@@ -21,6 +21,7 @@ namespace ffsb {
 struct ErodeArgs {
     int width, height, n_frames, slot0;
     int words_per_row;
+    uint32_t inv_wpr;            // floor(2^32 / words_per_row) + 1, or 0: divide
     const uint32_t* mask_bits;   // validity plane of the dataset
     const uint32_t* d_bits;      // pass-1 plane(s) (ext1)
     uint32_t* b_bits;            // output plane(s) (ext2): valid and not in the core
@@ -46,7 +47,7 @@ __global__ void __launch_bounds__(256) erode_kernel(const ErodeArgs a) {
     // atomic per warp and word row instead of one per core pixel on a single address)
     for (int t0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); t0 < n_words; t0 += gridDim.x * blockDim.x) {
         const int t = t0 + lane;
-        const int row = t / wpr, wi = t - row * wpr;
+        const int row = a.inv_wpr ? (int)__umulhi((uint32_t)t, a.inv_wpr) : t / wpr, wi = t - row * wpr;
         const bool in_plane = t < n_words;
         uint32_t core = 0;
         if (in_plane && wi > last_word) {

@@ -88,3 +88,18 @@ def test_oracle_decoder_matches_original_and_product_host_decoder(dtype):
         oracle.bslz4_decode(chunk[:-9], dtype, 5000)
     with pytest.raises(ValueError):
         oracle.bslz4_decode(chunk, dtype, 5008)
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+def test_crafted_sequences_host_decoder_and_oracle(dtype):
+    """LZ4 blocks written sequence by sequence (bslz4_ref.crafted_lz4_block: every literal length,
+    match length and offset class the decoders distinguish), expected elements from the
+    generator's own byte-wise expansion and an independent numpy bit un-transpose."""
+    from bslz4_ref import crafted_chunk
+    from oracle import oracle
+    rng = np.random.default_rng(2026)
+    for _ in range(4):
+        chunk, want = crafted_chunk(rng, dtype, 5)
+        assert np.array_equal(oracle.bslz4_decode(chunk, dtype, want.size).reshape(-1), want)
+        rc, out = decode(chunk, want.size, dtype)
+        assert rc == 0 and np.array_equal(out, want)

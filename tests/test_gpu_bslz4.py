@@ -137,3 +137,24 @@ def test_header_block_size_zero_means_the_default(dtype):
     assert np.array_equal(oracle.bslz4_decode(bytes(chunk), dtype, f.size).reshape(f.shape), f)
     with Spotfinder(g.width, g.height, dtype, mask, n_slots=1) as sf:
         assert np.array_equal(sf.decode_chunk(bytes(chunk)), f)
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.uint32])
+def test_crafted_sequences(dtype):
+    """Every branch of the device decoder's sequence loop on purpose: LZ4 blocks written sequence
+    by sequence (literal runs 0..14 from the register window, 15+ through the extension loop and
+    the global copy; match lengths around the token limit, one extension byte, an extension byte of
+    255, the 128-byte short-copy limit; offsets 1/2/4 runs, other powers of two, odd short periods,
+    periods just above a 32-byte round, both sides of 132).  Expected elements come from the
+    generator's byte-wise expansion and a numpy bit un-transpose, independent of every decoder."""
+    from bslz4_ref import crafted_chunk
+    rng = np.random.default_rng(77)
+    es = np.dtype(dtype).itemsize
+    n_blocks = 24
+    w = 256
+    h = n_blocks * (8192 // es) // w
+    with Spotfinder(w, h, dtype, None, n_slots=1) as sf:
+        for _ in range(6):
+            chunk, want = crafted_chunk(rng, dtype, n_blocks)
+            assert np.array_equal(sf.decode_chunk(chunk).reshape(-1), want)
+            assert np.array_equal(host_decode(chunk, want.size, dtype), want)
