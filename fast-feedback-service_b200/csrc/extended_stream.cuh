@@ -169,7 +169,11 @@ __device__ __noinline__ uint2 ext_row_slow(const ThreshArgs* __restrict__ ap, co
 }
 
 template <typename PixelT, int STAGES, int WARPS>
+#ifdef EXT_MAXNREG  // A/B builds: an explicit register cap instead of the resident-CTA hint
+__global__ void __maxnreg__(EXT_MAXNREG)
+#else
 __global__ void __launch_bounds__(WARPS * 32, WARPS == 3 ? EXT_MIN_CTAS : 1)
+#endif
   ext_pass1_kernel(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_info4,
                    const __grid_constant__ ThreshArgs a) {
     using G = FusedGeo<PixelT>;
