@@ -37,7 +37,7 @@ static int bslz4_setup(ffs_ctx* c) {
     c->chunk_stride = c->table_cap + c->chunk_cap;
     FFS_CK(c, cudaHostAlloc(&c->h_chunks, c->chunk_stride * S, cudaHostAllocDefault));
     FFS_CK(c, cudaMalloc(&c->d_chunks, c->chunk_stride * S + 64));
-    FFS_CK(c, cudaMalloc(&c->d_dec_status, sizeof(unsigned) * S));
+    FFS_CK(c, cudaMalloc(&c->d_dec_status, 2 * sizeof(unsigned) * S));  // per slot {status, work counter}
     FFS_CK(c, cudaHostAlloc(&c->h_dec_status, sizeof(unsigned) * S, cudaHostAllocDefault));
     memset(c->h_dec_status, 0, sizeof(unsigned) * S);
     return FFS_OK;
@@ -102,7 +102,11 @@ static int bslz4_index(ffs_ctx* c, int slot, const uint8_t* chunk, size_t len, B
 }
 
 static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st) {
+#ifdef BSLZ4_PERSISTENT
+    constexpr int kWarps = 28;  // 28 x 8208 B of shared memory: one CTA per SM
+#else
     constexpr int kWarps = 2;
+#endif
     Bslz4Args a{};
     a.chunk = bslz4_d_chunk(c, slot);
     a.dyn = reinterpret_cast<const Bslz4Dyn*>(a.chunk) - 1;
@@ -111,9 +115,15 @@ static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st
     a.width = c->p.width;
     a.elem_size = c->p.bytes_per_pixel;
     a.inv_width = (uint32_t)((1ull << 32) / c->p.width) + 1u;
-    a.status = c->d_dec_status + slot;
+    a.status = c->d_dec_status + 2 * slot;
     const int smem = kWarps * kBslz4SmemPerWarp;
+#ifdef BSLZ4_PERSISTENT
+    int n_sm = 0;
+    FFS_CK(c, cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, c->p.device));
+    const unsigned grid = std::max(1u, std::min((unsigned)n_sm, (n_blocks + kWarps - 1) / kWarps));
+#else
     const unsigned grid = std::max(1u, (n_blocks + kWarps - 1) / kWarps);
+#endif
     static bool attr_done[64][2] = {};
     const int pi = c->p.bytes_per_pixel == 2 ? 0 : 1;
     if (!attr_done[c->p.device & 63][pi]) {
@@ -125,7 +135,7 @@ static int bslz4_launch(ffs_ctx* c, int slot, uint32_t n_blocks, cudaStream_t st
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done[c->p.device & 63][pi] = true;
     }
-    FFS_CK(c, cudaMemsetAsync(c->d_dec_status + slot, 0, sizeof(unsigned), st));
+    FFS_CK(c, cudaMemsetAsync(c->d_dec_status + 2 * slot, 0, 2 * sizeof(unsigned), st));
     if (pi == 0)
         bslz4_decode_kernel<uint16_t, kWarps><<<grid, kWarps * 32, smem, st>>>(a);
     else
@@ -211,7 +221,7 @@ extern "C" int ffs_decode_chunk_device(ffs_ctx* c, int slot, const void* chunk, 
     rc = bslz4_launch(c, slot, dyn.n_blocks, st);
     if (rc) return rc;
     unsigned status = 0;
-    FFS_CK(c, cudaMemcpyAsync(&status, c->d_dec_status + slot, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    FFS_CK(c, cudaMemcpyAsync(&status, c->d_dec_status + 2 * slot, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
     FFS_CK(c, cudaStreamSynchronize(st));
     if (status) return FFS_ERR_FORMAT;
     if (frame_out) {

@@ -108,7 +108,7 @@ static int slot_work(ffs_ctx* c, int slot, int mode, uint32_t n_blocks, cudaStre
     } else {
         int rc = bslz4_launch(c, slot, n_blocks, st);
         if (rc) return rc;
-        FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + slot, sizeof(unsigned),
+        FFS_CK(c, cudaMemcpyAsync(c->h_dec_status + slot, c->d_dec_status + 2 * slot, sizeof(unsigned),
                                   cudaMemcpyDeviceToHost, st));
     }
     if (tev) FFS_CK(c, cudaEventRecord(tev[1], st));

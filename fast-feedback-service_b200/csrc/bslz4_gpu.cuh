@@ -49,7 +49,8 @@ struct Bslz4Args {
     uint32_t width;
     uint32_t elem_size;         // 2 or 4
     uint32_t inv_width;         // floor(2^32 / width) + 1: n / width == umulhi(n, inv_width) for n*width < 2^32
-    unsigned int* status;       // set to nonzero on malformed input
+    unsigned int* status;       // set to nonzero on malformed input; status[1] = work counter of the
+                                // persistent variant (BSLZ4_PERSISTENT), zeroed with it before every launch
 };
 
 // 8x8 bit-matrix transpose of the 64-bit value hi:lo (byte r = row r).
@@ -299,12 +300,18 @@ extern "C" int ffs_debug_bslz4_timeline(void* out, size_t bytes) {
 #endif
 // grid: ceil(n_blocks / WARPS) CTAs of WARPS warps; dynamic smem WARPS * kBslz4SmemPerWarp.
 template <typename PixelT, int WARPS>
+#ifdef BSLZ4_PERSISTENT
+__global__ void __launch_bounds__(WARPS * 32, 1) bslz4_decode_kernel(const Bslz4Args a) {
+#else
 __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kernel(const Bslz4Args a) {
+#endif
     extern __shared__ __align__(16) uint8_t bsmem[];
     const Bslz4Dyn dyn = *a.dyn;
     const uint2* blocks = reinterpret_cast<const uint2*>(a.dyn) - dyn.n_blocks;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifndef BSLZ4_PERSISTENT
     const uint32_t w_id = blockIdx.x * WARPS + warp;
+#endif
     constexpr int ES = (int)sizeof(PixelT);
     uint8_t* out = bsmem + (size_t)warp * kBslz4SmemPerWarp;
 
@@ -318,11 +325,24 @@ __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kerne
         const uint32_t row = e / a.width, col = e % a.width;
         reinterpret_cast<PixelT*>(a.frame + (size_t)row * a.pitch)[col] = v;
     }
+#ifdef BSLZ4_PERSISTENT
+    // one CTA per SM with as many warps as its shared memory holds; every warp pulls the next block of
+    // the work order until none is left (no second wave of CTAs waiting for a whole CTA to retire)
+#define BSLZ4_NEXT continue
+    for (;; __syncwarp()) {
+    uint32_t w_id = 0;
+    if (lane == 0) w_id = atomicAdd(a.status + 1, 1u);
+    w_id = __shfl_sync(0xffffffffu, w_id, 0);
+    if (w_id >= dyn.n_blocks) break;
+#else
+#define BSLZ4_NEXT return
     if (w_id >= dyn.n_blocks) return;
+    {
+#endif
     const uint32_t b = (reinterpret_cast<const uint32_t*>(blocks) - dyn.n_blocks)[w_id];  // longest payload first
     if (b >= dyn.n_blocks) {
         if (lane == 0) atomicExch(a.status, 3u);
-        return;
+        BSLZ4_NEXT;
     }
     const uint2 blk = blocks[b];
     const int n_el = (b + 1 == dyn.n_blocks) ? (int)dyn.last_elems : (int)dyn.block_elems;
@@ -330,7 +350,7 @@ __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kerne
     const int in_len = (int)blk.y;
     if (in_len > kBslz4InBytes - 32 || out_len > kBslz4MaxBlockBytes) {
         if (lane == 0) atomicExch(a.status, 1u);
-        return;
+        BSLZ4_NEXT;
     }
     const uint8_t* in = a.chunk + blk.x;
 #ifdef BSLZ4_TIMELINE
@@ -339,7 +359,7 @@ __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kerne
     // 2. LZ4
     if (!lz4_warp_decode(in, in_len, out, out_len, lane)) {
         if (lane == 0) atomicExch(a.status, 2u);
-        return;
+        BSLZ4_NEXT;
     }
     __syncwarp();
 #ifdef BSLZ4_TIMELINE
@@ -438,6 +458,8 @@ __global__ void __launch_bounds__(WARPS * 32, BSLZ4_MIN_CTAS) bslz4_decode_kerne
         g_bslz4_timeline[w_id] = make_uint4(tl0, tl1, tl_now(), b | (smid << 16));
     }
 #endif
+    }  // one block
+#undef BSLZ4_NEXT
 }
 
 }  // namespace ffsb

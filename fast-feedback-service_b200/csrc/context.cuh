@@ -118,7 +118,7 @@ struct ffs_ctx {
     uint32_t max_blocks = 0;
     uint8_t* h_chunks = nullptr;      // pinned, n_slots * chunk_stride
     uint8_t* d_chunks = nullptr;
-    unsigned int* d_dec_status = nullptr;  // n_slots
+    unsigned int* d_dec_status = nullptr;  // n_slots x {status, work counter}
     unsigned int* h_dec_status = nullptr;  // pinned
 
     // TMA descriptors
